@@ -1,0 +1,332 @@
+// probtalk_b200 -- the tensor-core contraction engine (sm_100a: TMA + tcgen05 + TMEM).
+//
+// One persistent, warp-specialised kernel computes
+//     out[row(m), n] = epilogue( sum_{tap, c} A[m*1 + base_row + tap/s][(tap%s)*C + c] * W[n][tap*C + c] )
+// which covers every dense op on ProbTalk's inference path with ONE code path:
+//   * nn.Linear / 1x1 Conv1d               taps = 1
+//   * Conv1d k3 s1 p1, k7 s1 p3            taps = k,  s = 1   (activations are channels-last with zero halo rows)
+//   * Conv1d k4 s2 p1                      taps = 4,  s = 2   (A viewed as [rows/2, 2C]: tap j -> row j/2, column half j%2)
+//   * ConvTranspose1d k4 s2 p1             two launches (even / odd output phase), taps = 2, output row stride 2
+// (reference layers: nets/spg/vqvae_modules.py:107-245, nets/inpainting/gated_pixelcnn_1d.py:39-83,
+//  nets/inpainting/PTransformer.py:284-372).  A is bf16 [rows, C] row-major (K-major), W is bf16 [N, taps*C]
+// K-major; accumulation is fp32 in TMEM.
+//
+// Warp roles (256 threads, 1 CTA / SM, persistent over 128 x BN output tiles):
+//   warp 0  TMA producer: per K-step one 128x64 A box + one BNx64 W box (SWIZZLE_128B) into a smem ring
+//   warp 1  MMA issuer  : one thread, 4 x tcgen05.mma (K=16 each) per K-step, tcgen05.commit frees the slot
+//   warp 2  TMEM allocator (2 accumulator stages x BN columns)
+//   warps 4-7 epilogue  : tcgen05.ld (lane = output row), bias / residual / activation, direct global stores
+// so the epilogue of tile i overlaps the main loop of tile i+1.
+#include <cuda.h>
+#include "pt_common.cuh"
+#include "pt_host.h"
+#include "pt_gemm.h"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
+constexpr int kThreads = 256;
+constexpr int kEpiWarp0 = 4;
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
+  static constexpr uint32_t kBBytes = BN * BK * 2;          // 16 / 32 KB
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr uint32_t kTmemCols = 2 * BN;             // double-buffered accumulator
+  static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256;
+};
+
+struct GemmKernelArgs {
+  int M, N_tiles, K_iters;        // K_iters = taps * (C / 64)
+  int c_iters;                    // C / 64
+  int C;                          // channels per tap
+  int s;                          // input stride (1 or 2)
+  int base_row;
+  int rows_per_sample, t_valid;
+  int n_valid;
+  long long oss, ors, ocs;        // output strides (elements): sample, row-in-sample, column
+  long long rss, rrs;             // residual strides (elements): sample, row-in-sample (column stride 1)
+  void* out;
+  const float* bias;
+  const void* residual;
+  int out_f32, res_f32;
+  int act;                        // pt_gemm.h: PT_ACT_*
+  float slope;
+  int m_tiles;
+};
+
+__device__ __forceinline__ float apply_act(float v, int act, float slope) {
+  if (act == PT_ACT_RELU) return fmaxf(v, 0.f);
+  if (act == PT_ACT_LEAKY) return v > 0.f ? v : v * slope;
+  return v;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+            const GemmKernelArgs p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)C::kStages * C::kStageBytes);
+  uint64_t* full = bars;                         // [kStages]
+  uint64_t* empty = bars + C::kStages;           // [kStages]
+  uint64_t* tmem_full = bars + 2 * C::kStages;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;          // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles_total = p.m_tiles * p.N_tiles;
+
+  if (warp == 0 && lane == 0) {
+    pt::tma_prefetch_desc(&tmap_a);
+    pt::tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], 4); }
+    pt::fence_mbar_init();
+  }
+  if (warp == 2) {
+    pt::tmem_alloc(tmem_slot, C::kTmemCols);
+    pt::tmem_relinquish();
+  }
+  pt::tc_fence_before();
+  __syncthreads();
+  pt::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+        const int m0 = (tile / p.N_tiles) * BM, n0 = (tile % p.N_tiles) * BN;
+        for (int kk = 0; kk < p.K_iters; ++kk) {
+          const int tap = kk / p.c_iters, cc = kk - tap * p.c_iters;
+          pt::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+          pt::mbar_expect_tx(&full[stage], C::kStageBytes);
+          pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
+          pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = pt::umma_idesc_bf16(BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+        pt::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        pt::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kk = 0; kk < p.K_iters; ++kk) {
+          pt::mbar_wait(&full[stage], phase);
+          pt::tc_fence_after();
+          const uint32_t sa = pt::smem_u32(smem + (size_t)stage * C::kStageBytes);
+          const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
+                          (kk | k) ? 1u : 0u);
+          }
+          pt::umma_commit(&empty[stage]);                 // slot reusable once these MMAs have read it
+          if (kk == p.K_iters - 1) pt::umma_commit(&tmem_full[acc]);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // ------------------------------------------------------------ epilogue
+    const int q = warp & 3;                              // TMEM lane quadrant this warp may touch
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+      const int m0 = (tile / p.N_tiles) * BM, n0 = (tile % p.N_tiles) * BN;
+      const int m = m0 + q * 32 + lane;
+      const int b = m / p.rows_per_sample, t = m - b * p.rows_per_sample;
+      const bool row_ok = (m < p.M) && (t < p.t_valid);
+      const long long obase = (long long)b * p.oss + (long long)t * p.ors;
+      const long long rbase = (long long)b * p.rss + (long long)t * p.rrs;
+      pt::mbar_wait(&tmem_full[acc], acc_phase);
+      pt::tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        pt::tmem_ld32(t_row + c0, v);
+        pt::tmem_ld_wait();
+        const int n = n0 + c0;
+        if (row_ok && n < p.n_valid) {
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + n + i);
+          }
+          if (p.residual) {
+            if (p.res_f32) {
+              const float4* r = reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + rbase + n);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                float4 x = __ldg(r + i);
+                f[4 * i] += x.x; f[4 * i + 1] += x.y; f[4 * i + 2] += x.z; f[4 * i + 3] += x.w;
+              }
+            } else {
+              const uint4* r = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rbase + n);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                uint4 x = __ldg(r + i);
+                const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[j]);
+                  f[8 * i + 2 * j] += __bfloat162float(h.x);
+                  f[8 * i + 2 * j + 1] += __bfloat162float(h.y);
+                }
+              }
+            }
+          }
+          if (p.act == PT_ACT_GATE) {
+            // interleaved columns (a0,b0,a1,b1,...) -> tanh(a) * sigmoid(b), 16 outputs at column n/2
+            float gt[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) gt[i] = tanhf(f[2 * i]) * (1.f / (1.f + __expf(-f[2 * i + 1])));
+            __nv_bfloat16* o = static_cast<__nv_bfloat16*>(p.out) + obase + (n >> 1);
+            uint4 w0 = make_uint4(pt::pack_bf16x2(gt[0], gt[1]), pt::pack_bf16x2(gt[2], gt[3]),
+                                  pt::pack_bf16x2(gt[4], gt[5]), pt::pack_bf16x2(gt[6], gt[7]));
+            uint4 w1 = make_uint4(pt::pack_bf16x2(gt[8], gt[9]), pt::pack_bf16x2(gt[10], gt[11]),
+                                  pt::pack_bf16x2(gt[12], gt[13]), pt::pack_bf16x2(gt[14], gt[15]));
+            reinterpret_cast<uint4*>(o)[0] = w0;
+            reinterpret_cast<uint4*>(o)[1] = w1;
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = apply_act(f[i], p.act, p.slope);
+            if (p.ocs == 1 && n + 32 <= p.n_valid) {
+              if (p.out_f32) {
+                float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + obase + n);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+              } else {
+                uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + obase + n);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                  o[i] = make_uint4(pt::pack_bf16x2(f[8 * i], f[8 * i + 1]), pt::pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                                    pt::pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pt::pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+              }
+            } else {
+              // strided / ragged columns: lanes hold consecutive rows, so a channel-first output is coalesced
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                if (n + i < p.n_valid) {
+                  const long long off = obase + (long long)(n + i) * p.ocs;
+                  if (p.out_f32) static_cast<float*>(p.out)[off] = f[i];
+                  else static_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(f[i]);
+                }
+              }
+            }
+          }
+        }
+      }
+      pt::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) pt::mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  pt::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) pt::tmem_dealloc(tmem_base, C::kTmemCols);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 row-major [rows, cols] matrix with row pitch `pitch` elements; box = 64 columns x box_rows rows
+int make_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols, long long pitch, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return pt::fail("cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return pt::fail("cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld pitch=%lld base=%p", (int)r, rows, cols,
+                    pitch, base);
+  return 0;
+}
+
+template <int BN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
+    attr_done = true;
+  }
+  const int tiles = ka.m_tiles * ka.N_tiles;
+  const int grid = tiles < sms ? tiles : sms;
+  gemm_kernel<BN><<<grid, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, ka);
+  PT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
+  if (!d) return pt::fail("pt_gemm_bf16: null descriptor");
+  if (d->M <= 0 || d->N <= 0) return 0;
+  if (!d->a || !d->w || !d->out) return pt::fail("pt_gemm_bf16: null operand");
+  if (d->C <= 0 || d->C % BK) return pt::fail("pt_gemm_bf16: C (%d) must be a positive multiple of 64", d->C);
+  if (d->taps < 1 || (d->s != 1 && d->s != 2)) return pt::fail("pt_gemm_bf16: bad taps/stride %d/%d", d->taps, d->s);
+  if (d->N % 128) return pt::fail("pt_gemm_bf16: N (%d) must be padded to a multiple of 128", d->N);
+  if (d->n_valid <= 0 || d->n_valid > d->N) return pt::fail("pt_gemm_bf16: bad n_valid %d", d->n_valid);
+  if (d->rows_per_sample <= 0) return pt::fail("pt_gemm_bf16: rows_per_sample must be positive");
+  if (d->act == PT_ACT_GATE && (d->out_f32 || d->ocs != 1 || d->residual || (d->n_valid & 31)))
+    return pt::fail("pt_gemm_bf16: gated epilogue needs bf16 row-major output, no residual, n_valid %% 32 == 0");
+  if ((reinterpret_cast<uintptr_t>(d->a) | reinterpret_cast<uintptr_t>(d->w)) & 15)
+    return pt::fail("pt_gemm_bf16: operands must be 16-byte aligned");
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+
+  CUtensorMap ta, tb;
+  // A viewed as [a_rows / s, s * C] (tap j of a stride-2 conv = row j/2, column half j%2)
+  if (d->a_rows % d->s) return pt::fail("pt_gemm_bf16: a_rows (%lld) not divisible by stride", d->a_rows);
+  if (make_tmap(&ta, d->a, d->a_rows / d->s, (long long)d->s * d->C, (long long)d->s * d->a_pitch, BM)) return 1;
+  const int BN = (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
+  if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, BN)) return 1;
+
+  GemmKernelArgs ka;
+  ka.M = d->M; ka.N_tiles = d->N / BN; ka.c_iters = d->C / BK; ka.K_iters = d->taps * ka.c_iters;
+  ka.C = d->C; ka.s = d->s; ka.base_row = d->base_row;
+  ka.rows_per_sample = d->rows_per_sample; ka.t_valid = d->t_valid; ka.n_valid = d->n_valid;
+  ka.oss = d->oss; ka.ors = d->ors; ka.ocs = d->ocs; ka.rss = d->rss; ka.rrs = d->rrs;
+  ka.out = d->out; ka.bias = d->bias; ka.residual = d->residual; ka.out_f32 = d->out_f32; ka.res_f32 = d->res_f32;
+  ka.act = d->act; ka.slope = d->slope; ka.m_tiles = (d->M + BM - 1) / BM;
+  cudaStream_t st = (cudaStream_t)stream;
+  return BN == 256 ? launch<256>(ta, tb, ka, sms, st) : launch<128>(ta, tb, ka, sms, st);
+}

@@ -1,0 +1,123 @@
+"""Thin torch-tensor wrappers over the C ABI (``include/probtalk_b200.h``).
+
+torch is used for device memory and streams only; all arithmetic happens in the CUDA library.
+Every wrapper requires CUDA tensors and raises if the library is missing (no CPU fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import GemmDesc, check
+
+ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_GATE = 0, 1, 2, 3
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.PtError("probtalk_b200 ops need CUDA tensors (no CPU fallback)")
+
+
+def pq_search(z: torch.Tensor, codebooks: torch.Tensor, want_gap: bool = False, score_dump: bool = False,
+              count_rescored: bool = False):
+    """Nearest-code search.  z [B, G*D, W] fp32 (any strides), codebooks [G, K, D] fp32.
+    Returns idx int64 [B, W, G] (+ gap fp32 [B, W, G], + scores [B, W, G, K], + n_rescored tensor).
+    Mirrors ProductQuantization.get_code_indices (reference nets/spg/vqvae_modules.py:546-555)."""
+    _need_cuda(z, codebooks)
+    assert z.dtype == torch.float32 and codebooks.dtype == torch.float32 and z.dim() == 3
+    G, K, D = codebooks.shape
+    B, Cc, W = z.shape
+    assert Cc == G * D, "z has %d channels, codebooks cover %d" % (Cc, G * D)
+    codebooks = codebooks.contiguous()
+    idx = torch.empty((B, W, G), dtype=torch.int64, device=z.device)
+    gap = torch.empty((B, W, G), dtype=torch.float32, device=z.device) if want_gap else None
+    dump = torch.empty((B, W, G, K), dtype=torch.float32, device=z.device) if score_dump else None
+    nres = torch.zeros((1,), dtype=torch.int32, device=z.device) if count_rescored else None
+    sb, sc, sw = z.stride()
+    check(_lib.lib().pt_pq_search(z.data_ptr(), sb, sc, sw, B, W, G, K, D, codebooks.data_ptr(), idx.data_ptr(),
+                                  _ptr(gap), _ptr(dump), _ptr(nres), _stream()), "pt_pq_search")
+    out = [idx]
+    if want_gap:
+        out.append(gap)
+    if score_dump:
+        out.append(dump)
+    if count_rescored:
+        out.append(nres)
+    return out[0] if len(out) == 1 else tuple(out)
+
+
+def pq_gather(idx: torch.Tensor, codebooks: torch.Tensor, out: torch.Tensor = None, channels_last: bool = False,
+              dtype=torch.float32):
+    """Codebook gather: idx [B, W, G] -> quantized [B, G*D, W] (reference layout, default) or
+    [B, W, G*D] (channels_last).  Mirrors ProductQuantization.quantize_all (vqvae_modules.py:557-564)
+    followed by the transpose of predictor.py:440."""
+    _need_cuda(idx, codebooks)
+    G, K, D = codebooks.shape
+    B, W, G2 = idx.shape
+    assert G2 == G and idx.dtype in (torch.int64, torch.int32)
+    idx = idx.contiguous()
+    codebooks = codebooks.contiguous()
+    if out is None:
+        shape = (B, W, G * D) if channels_last else (B, G * D, W)
+        out = torch.empty(shape, dtype=dtype, device=idx.device)
+    if channels_last:
+        os_b, os_w, os_c = out.stride()
+    else:
+        os_b, os_c, os_w = out.stride()
+    bad = torch.zeros((1,), dtype=torch.int32, device=idx.device)
+    check(_lib.lib().pt_pq_gather(idx.data_ptr(), int(idx.dtype == torch.int64), codebooks.data_ptr(), out.data_ptr(),
+                                  int(out.dtype == torch.bfloat16), os_b, os_c, os_w, B, W, G, K, D, bad.data_ptr(),
+                                  _stream()), "pt_pq_gather")
+    return out, bad
+
+
+def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int, taps: int = 1, s: int = 1,
+         base_row: int = 0, rows_per_sample: int = None, t_valid: int = None, n_valid: int = None,
+         oss: int = 0, ors: int = None, ocs: int = 1, out_offset: int = 0, bias: torch.Tensor = None,
+         residual: torch.Tensor = None, rss: int = 0, rrs: int = 0, res_offset: int = 0, act: int = ACT_NONE,
+         slope: float = 0.2, a_rows: int = None, a_pitch: int = None, a_offset: int = 0):
+    """Launch the tensor-core contraction engine (see pt_gemm_bf16 in include/probtalk_b200.h).
+    ``a`` / ``out`` / ``residual`` are flat device buffers; offsets are in elements."""
+    _need_cuda(a, w, out, bias, residual)
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and w.dim() == 2
+    N = w.shape[0]
+    assert w.shape[1] == taps * C_ and w.is_contiguous()
+    d = GemmDesc()
+    d.a = a.data_ptr() + 2 * a_offset
+    d.a_pitch = a_pitch if a_pitch is not None else C_
+    d.a_rows = a_rows if a_rows is not None else (a.numel() - a_offset) // d.a_pitch
+    d.w = w.data_ptr()
+    d.M, d.N, d.C, d.taps, d.s = M, N, C_, taps, s
+    d.base_row = base_row
+    d.rows_per_sample = rows_per_sample if rows_per_sample is not None else max(M, 1)
+    d.t_valid = t_valid if t_valid is not None else d.rows_per_sample
+    d.n_valid = n_valid if n_valid is not None else N
+    d.out = out.data_ptr() + out.element_size() * out_offset
+    d.oss, d.ors, d.ocs = oss, (ors if ors is not None else d.n_valid), ocs
+    d.out_f32 = int(out.dtype == torch.float32)
+    assert out.dtype in (torch.float32, torch.bfloat16)
+    d.bias = _ptr(bias)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() >= N
+    if residual is not None:
+        assert residual.dtype in (torch.float32, torch.bfloat16)
+        d.residual = residual.data_ptr() + residual.element_size() * res_offset
+        d.res_f32 = int(residual.dtype == torch.float32)
+    else:
+        d.residual = None
+        d.res_f32 = 0
+    d.rss, d.rrs = rss, rrs
+    d.act, d.slope = act, slope
+    check(_lib.lib().pt_gemm_bf16(C.byref(d), _stream()), "pt_gemm_bf16")
+    return out
