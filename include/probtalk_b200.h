@@ -87,6 +87,59 @@ typedef struct pt_gemm_desc {
 
 int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Multi-head attention core (softmax(q k^T * scale) v), bf16 in/out, fp32 softmax and accumulation.
+ * Replaces the scaled-dot-product part of nn.MultiheadAttention as called at
+ * nets/inpainting/PTransformer.py:340 (self) and :350 (cross); in/out projections are pt_gemm_bf16.
+ *   q   rows b*Nq + i, head h at columns [h*head_dim, (h+1)*head_dim), row stride q_stride elements
+ *   k,v rows b*Nk + j, same column rule, strides k_stride / v_stride
+ *   out rows b*Nq + i, row stride out_stride
+ * head_dim must be 64, 1 <= Nk <= 192, Nq <= 1024. */
+int pt_attention(const void* q, long long q_stride, const void* k, long long k_stride, const void* v,
+                 long long v_stride, void* out, long long out_stride, int B, int heads, int head_dim, int Nq, int Nk,
+                 float scale, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Layout kernels between the reference's channel-first fp32 tensors [B, C, T] and the engine's
+ * channels-last bf16 rows [B, Tp, Cp] (H zero halo rows in front of every sample).
+ * pt_pack_rows writes channels [c_off, c_off + C) of rows H .. H+T-1:
+ *   mode 0: src                     (audio features, predictor.py:428 / refiner.py:544)
+ *   mode 1: src * mask              (input_poses = gt_poses * mask, predictor.py:425)
+ *   mode 2: src * mask + interp(pred, T) * (1 - mask)     (refiner.py:524-529, linear F.interpolate)
+ * pt_pack_mask writes the mask channel (onehot = 0; predictornet.py:85) or the two one-hot channels
+ * (onehot = 1; RTransformer.py:218). */
+int pt_pack_rows(const float* src, const float* mask, const float* pred, int pred_T, void* dst_bf16, int B, int C,
+                 int T, int Tp, int H, int Cp, int c_off, int mode, void* stream);
+int pt_pack_mask(const float* mask, void* dst_bf16, int B, int T, int Tp, int H, int Cp, int c_off, int onehot,
+                 void* stream);
+
+/* out = known * mask^mask_pow + interp(pred, T) * (1 - mask), all fp32 channel-first [B, C, T] (pred [B, C, pred_T]).
+ * mask_pow = 2: predictor.py:445-446 ((gt*mask)*mask + ...);  mask_pow = 1: refiner.py:553. */
+int pt_interp_blend(const float* known, const float* mask, const float* pred, int pred_T, float* out, int B, int C,
+                    int T, int mask_pow, void* stream);
+
+/* nn.LayerNorm(512, eps 1e-5) over rows (norm1/2/3, PTransformer.py:329-331): fp32 in, fp32 and/or bf16 out. */
+int pt_layernorm512(const float* in, const float* gamma, const float* beta, float* out_f32, void* out_bf16, int M,
+                    void* stream);
+
+/* StylizationBlock_V3 'sb' branch before its output Linear (PTransformer.py:134-139):
+ *   out = SiLU( LN(in) * (1 + scale) + shift ),  [scale | shift] = mod[labels[row / rows_per_sample]]  (mod: [n_classes, 1024] fp32,
+ *   the emb_layers_2 Linear applied to SiLU(class_embed) -- precomputed per class by the host). */
+int pt_ln_mod_silu512(const void* in, int in_f32, const float* gamma, const float* beta, const float* mod,
+                      const int* labels, int rows_per_sample, void* out_bf16, int M, void* stream);
+
+/* Token embedding + positional encodings (PTransformer.py:659-679): row r -> float32(emb[tokens[r]] + pe64[r % N]),
+ * the fp64 add + fp32 round of the reference.  bad_count (or NULL) counts tokens outside [0, n_emb). */
+int pt_embed_tokens512(const int* tokens, const float* emb, int n_emb, const double* pe64, int N, float* out_f32,
+                       void* out_bf16, int M, int* bad_count, void* stream);
+
+/* One MaskGIT refinement step: PTransformer.sample_good loop body (PTransformer.py:603-638) and
+ * mask_by_random_topk (:696-704).  logits fp32 [B, N, n_codes]; cur_ids/next_ids int32 [B, N] (may alias);
+ * u uniform(0,1) and gumbel Gumbel(0,1) noise [B, N] supplied by the caller (the reference draws them from
+ * torch RNG streams that are not reproducible across devices); base_mask_len = floor(N * cos(pi/2 * (step+1)/T)). */
+int pt_maskgit_step(const float* logits, const int* cur_ids, const float* u, const float* gumbel, int* next_ids,
+                    int B, int N, int n_codes, int mask_id, int base_mask_len, float temperature, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

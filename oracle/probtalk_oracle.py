@@ -344,10 +344,16 @@ def categorical_from_uniform(logits, u):
     ``Categorical(logits=logits).sample()`` (PTransformer.py:607) whose RNG stream cannot be
     reproduced across devices; the CUDA sampler uses the same rule with the same ``u``."""
     p = torch.exp(logits - logits.max(-1, keepdim=True).values)
-    cdf = torch.cumsum(p, dim=-1)
+    K = logits.shape[-1]
+    acc = torch.zeros_like(p[..., 0])
+    cols = []
+    for k in range(K):                      # sequential fp32 running sum, index order
+        acc = acc + p[..., k]
+        cols.append(acc)
+    cdf = torch.stack(cols, dim=-1)
     thr = (u * cdf[..., -1]).unsqueeze(-1)
     k = (cdf <= thr).sum(-1)
-    return k.clamp_(max=logits.shape[-1] - 1)
+    return k.clamp_(max=K - 1)
 
 
 def maskgit_step(logits, cur_ids, step, T, u, gumbel):

@@ -104,37 +104,57 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   if (tid < kTileRows) s.sx2[tid] = 0.f;
   __syncthreads();
 
-  // ---- stage the codebook: warp per code row, lane holds k = 4*lane .. 4*lane+3 (coalesced 512 B)
-  for (int j = warp; j < kK; j += kThreads / 32) {
-    float4 c = __ldg(reinterpret_cast<const float4*>(cb + (size_t)j * kD) + lane);
-    float sq = fmaf(c.w, c.w, fmaf(c.z, c.z, fmaf(c.y, c.y, c.x * c.x)));
-    sq = warp_sum(sq);
-    if (lane == 0) {
-      s.sc2[j] = sq;
-      atomicMax(reinterpret_cast<int*>(&s.cmax), __float_as_int(sqrtf(sq)));   // non-negative floats order as ints
+  // ---- stage the codebook: warp per code row, lane holds k = 4*lane .. 4*lane+3 (coalesced 512 B).
+  // All 16 rows of a warp are requested before any is consumed (memory-level parallelism).
+  {
+    constexpr int kPerWarp = kK / (kThreads / 32);
+    float4 cv[kPerWarp];
+#pragma unroll
+    for (int i = 0; i < kPerWarp; ++i)
+      cv[i] = __ldg(reinterpret_cast<const float4*>(cb + (size_t)(warp + i * (kThreads / 32)) * kD) + lane);
+#pragma unroll
+    for (int i = 0; i < kPerWarp; ++i) {
+      const int j = warp + i * (kThreads / 32);
+      const float4 c = cv[i];
+      float sq = fmaf(c.w, c.w, fmaf(c.z, c.z, fmaf(c.y, c.y, c.x * c.x)));
+      sq = warp_sum(sq);
+      if (lane == 0) {
+        s.sc2[j] = sq;
+        atomicMax(reinterpret_cast<int*>(&s.cmax), __float_as_int(sqrtf(sq)));   // non-negative floats order as ints
+      }
+      __nv_bfloat16 h0 = __float2bfloat16_rn(c.x), h1 = __float2bfloat16_rn(c.y), h2 = __float2bfloat16_rn(c.z),
+                    h3 = __float2bfloat16_rn(c.w);
+      __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
+      uint2 hi = make_uint2(*reinterpret_cast<uint32_t*>(&a0), *reinterpret_cast<uint32_t*>(&a1));
+      uint2 lo = make_uint2(pt::pack_bf16x2(c.x - __bfloat162float(h0), c.y - __bfloat162float(h1)),
+                            pt::pack_bf16x2(c.z - __bfloat162float(h2), c.w - __bfloat162float(h3)));
+      const int k0 = lane * 4;                       // element index within the row
+      const uint32_t off = (k0 >> 6) * kAtomBytes + pt::sw128_offset(j, (k0 & 63) >> 3) + (k0 & 7) * 2;
+      *reinterpret_cast<uint2*>(s.ops[2] + off) = hi;
+      *reinterpret_cast<uint2*>(s.ops[3] + off) = lo;
     }
-    __nv_bfloat16 h0 = __float2bfloat16_rn(c.x), h1 = __float2bfloat16_rn(c.y), h2 = __float2bfloat16_rn(c.z),
-                  h3 = __float2bfloat16_rn(c.w);
-    __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
-    uint2 hi = make_uint2(*reinterpret_cast<uint32_t*>(&a0), *reinterpret_cast<uint32_t*>(&a1));
-    uint2 lo = make_uint2(pt::pack_bf16x2(c.x - __bfloat162float(h0), c.y - __bfloat162float(h1)),
-                          pt::pack_bf16x2(c.z - __bfloat162float(h2), c.w - __bfloat162float(h3)));
-    const int k0 = lane * 4;                       // element index within the row
-    const uint32_t off = (k0 >> 6) * kAtomBytes + pt::sw128_offset(j, (k0 & 63) >> 3) + (k0 & 7) * 2;
-    *reinterpret_cast<uint2*>(s.ops[2] + off) = hi;
-    *reinterpret_cast<uint2*>(s.ops[3] + off) = lo;
   }
 
-  // ---- stage the query rows
+  // ---- stage the query rows (row index math in 32 bits: tiles never span more than 2^31 rows)
+  const int W = a.W;
+  const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
   if (a.zs_c == 1) {
-    // channels-last rows: warp per row, float4 per lane
-    for (int r = warp; r < kTileRows; r += kThreads / 32) {
-      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    // channels-last rows: warp per row, float4 per lane; 16 rows in flight per warp
+    constexpr int kPerWarp = kTileRows / (kThreads / 32);
+    float4 xv[kPerWarp];
+#pragma unroll
+    for (int i = 0; i < kPerWarp; ++i) {
+      const int r = warp + i * (kThreads / 32);
+      xv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (r < nrows) {
-        const long long row = row0 + r;
-        const long long b = row / a.W, w = row % a.W;
-        x = __ldg(reinterpret_cast<const float4*>(a.z + b * a.zs_b + w * a.zs_w + (size_t)g * kD) + lane);
+        const int q = w0 + r, b = b0 + q / W, w = q % W;
+        xv[i] = __ldg(reinterpret_cast<const float4*>(a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD) + lane);
       }
+    }
+#pragma unroll
+    for (int i = 0; i < kPerWarp; ++i) {
+      const int r = warp + i * (kThreads / 32);
+      const float4 x = xv[i];
       float sq = warp_sum(fmaf(x.w, x.w, fmaf(x.z, x.z, fmaf(x.y, x.y, x.x * x.x))));
       if (lane == 0) s.sx2[r] = sq;
       __nv_bfloat16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y), h2 = __float2bfloat16_rn(x.z),
@@ -149,26 +169,32 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       *reinterpret_cast<uint2*>(s.ops[1] + off) = lo;
     }
   } else {
-    // channel-first (the reference's [B, C, W]): lanes walk consecutive rows (w contiguous), 8 channels each
-    for (int u = tid; u < kTileRows * (kD / 8); u += kThreads) {
-      const int r = u & (kTileRows - 1), chunk = u >> 7;   // chunk = 8 consecutive channels
-      float v[8];
+    // channel-first (the reference's [B, C, W]): lanes walk consecutive rows (w contiguous), 8 channels per
+    // unit; a thread's units share its row, and 4 units (32 loads) are in flight at a time
+    const int r = tid & (kTileRows - 1);
+    const bool live = r < nrows;
+    const int q = w0 + r, b = b0 + q / W, w = q % W;
+    const float* prow = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
+    float sq = 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = 0.f;
-      if (r < nrows) {
-        const long long row = row0 + r;
-        const long long b = row / a.W, w = row % a.W;
-        const float* p = a.z + b * a.zs_b + w * a.zs_w + ((size_t)g * kD + chunk * 8) * a.zs_c;
+    for (int h = 0; h < 2; ++h) {
+      float v[4][8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = __ldg(p + i * a.zs_c);
-        float sq = 0.f;
+      for (int u = 0; u < 4; ++u) {
+        const int chunk = (tid >> 7) + 2 * (h * 4 + u);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) sq = fmaf(v[i], v[i], sq);
-        atomicAdd(&s.sx2[r], sq);
+        for (int i = 0; i < 8; ++i) v[u][i] = live ? __ldg(prow + (size_t)(chunk * 8 + i) * a.zs_c) : 0.f;
       }
-      const uint32_t off = (chunk >> 3) * kAtomBytes + pt::sw128_offset(r, chunk & 7);
-      split_store(s.ops[0], s.ops[1], off, v);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int chunk = (tid >> 7) + 2 * (h * 4 + u);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sq = fmaf(v[u][i], v[u][i], sq);
+        const uint32_t off = (chunk >> 3) * kAtomBytes + pt::sw128_offset(r, chunk & 7);
+        split_store(s.ops[0], s.ops[1], off, v[u]);
+      }
     }
+    if (live) atomicAdd(&s.sx2[r], sq);
   }
   pt::fence_async_smem();        // generic-proxy smem writes -> visible to the tensor-core (async) proxy
   pt::tc_fence_before();
@@ -259,8 +285,8 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
     for (int rr = warp; rr < nrows; rr += kThreads / 32) {
       if (!s.ambiguous[rr]) continue;
       const long long row = row0 + rr;
-      const long long b = row / a.W, w = row % a.W;
-      const float* px = a.z + b * a.zs_b + w * a.zs_w + (size_t)g * kD * a.zs_c;
+      const int q = w0 + rr, b = b0 + q / W, w = q % W;
+      const float* px = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
       float x[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) x[i] = __ldg(px + (size_t)(lane + 32 * i) * a.zs_c);
