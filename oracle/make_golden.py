@@ -23,7 +23,7 @@ SEEDS = dict(vq=0, pred=1, ref=5)
 
 def main():
     vq, pst, rst = S.make_vq_state(SEEDS["vq"]), S.make_predictor_state(SEEDS["pred"]), S.make_refiner_state(SEEDS["ref"])
-    out = {"torch_version": torch.__version__, "threads": torch.get_num_threads(), "seeds": SEEDS}
+    out = {"torch_version": str(torch.__version__), "threads": torch.get_num_threads(), "seeds": SEEDS}
     ref_vq = RH.build_vqt(vq)
     ref_pred = RH.build_predictor(vq, pst)
     ref_ref = RH.build_refiner(vq, rst)

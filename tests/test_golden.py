@@ -13,7 +13,7 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.pt")
 
 @pytest.fixture(scope="module")
 def gold():
-    return torch.load(GOLD, map_location="cpu")
+    return torch.load(GOLD, map_location="cpu", weights_only=False)
 
 
 @pytest.fixture(scope="module")
