@@ -43,7 +43,7 @@ struct PqSmem {
   float rmin[kTileRows];
   float band[kTileRows];
   int ambiguous[kTileRows];
-  float cmax;
+  float cmax_w[kThreads / 32];
   uint64_t mma_done;
   uint32_t tmem_base;
   int n_amb;
@@ -81,6 +81,7 @@ struct PqArgs {
   int rows_per_tile;
 };
 
+template <bool kDump>
 __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   extern __shared__ uint8_t smem_raw[];
   PqSmem& s = *reinterpret_cast<PqSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -99,7 +100,6 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
     pt::mbar_init(&s.mma_done, 1);
     pt::fence_mbar_init();
     s.n_amb = 0;
-    s.cmax = 0.f;
   }
   if (tid < kTileRows) s.sx2[tid] = 0.f;
   __syncthreads();
@@ -112,16 +112,22 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i)
       cv[i] = __ldg(reinterpret_cast<const float4*>(cb + (size_t)(warp + i * (kThreads / 32)) * kD) + lane);
+    float sq[kPerWarp];
+#pragma unroll
+    for (int i = 0; i < kPerWarp; ++i)
+      sq[i] = fmaf(cv[i].w, cv[i].w, fmaf(cv[i].z, cv[i].z, fmaf(cv[i].y, cv[i].y, cv[i].x * cv[i].x)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int i = 0; i < kPerWarp; ++i) sq[i] += __shfl_xor_sync(0xffffffffu, sq[i], o);   // 16 independent chains
+    }
+    float wmax = 0.f;
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i) {
       const int j = warp + i * (kThreads / 32);
       const float4 c = cv[i];
-      float sq = fmaf(c.w, c.w, fmaf(c.z, c.z, fmaf(c.y, c.y, c.x * c.x)));
-      sq = warp_sum(sq);
-      if (lane == 0) {
-        s.sc2[j] = sq;
-        atomicMax(reinterpret_cast<int*>(&s.cmax), __float_as_int(sqrtf(sq)));   // non-negative floats order as ints
-      }
+      wmax = fmaxf(wmax, sq[i]);
+      if (lane == 0) s.sc2[j] = sq[i];
       __nv_bfloat16 h0 = __float2bfloat16_rn(c.x), h1 = __float2bfloat16_rn(c.y), h2 = __float2bfloat16_rn(c.z),
                     h3 = __float2bfloat16_rn(c.w);
       __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
@@ -133,6 +139,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       *reinterpret_cast<uint2*>(s.ops[2] + off) = hi;
       *reinterpret_cast<uint2*>(s.ops[3] + off) = lo;
     }
+    if (lane == 0) s.cmax_w[warp] = sqrtf(wmax);
   }
 
   // ---- stage the query rows (row index math in 32 bits: tiles never span more than 2^31 rows)
@@ -227,22 +234,36 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   const int r = (warp & 3) * 32 + lane;
   const int half = warp >> 2;
   const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16) + half * 64;
-  float m1 = INFINITY, m2 = INFINITY;
-  int i1 = 0;
+  // two independent (min, argmin, second-min) trackers (even / odd columns) for instruction-level parallelism
+  float ma1 = INFINITY, ma2 = INFINITY, mb1 = INFINITY, mb2 = INFINITY;
+  int ia = 0, ib = 1;
 #pragma unroll
   for (int c = 0; c < 2; ++c) {
     uint32_t v[32];
     pt::tmem_ld32(t_row + c * 32, v);
     pt::tmem_ld_wait();
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
+    for (int i = 0; i < 32; i += 2) {
       const int j = half * 64 + c * 32 + i;
-      const float sc = fmaf(-2.f, __uint_as_float(v[i]), s.sc2[j]);
-      if (a.score_dump && r < nrows) a.score_dump[((row0 + r) * a.G + g) * kK + j] = sc;
-      if (sc < m1) { m2 = m1; m1 = sc; i1 = j; }
-      else if (sc < m2) { m2 = sc; }
+      const float sa = fmaf(-2.f, __uint_as_float(v[i]), s.sc2[j]);
+      const float sb = fmaf(-2.f, __uint_as_float(v[i + 1]), s.sc2[j + 1]);
+      if constexpr (kDump) {
+        if (r < nrows) {
+          a.score_dump[((row0 + r) * a.G + g) * kK + j] = sa;
+          a.score_dump[((row0 + r) * a.G + g) * kK + j + 1] = sb;
+        }
+      }
+      ma2 = fminf(ma2, fmaxf(sa, ma1));           // second-min update, then min (strict < keeps the first index)
+      if (sa < ma1) { ma1 = sa; ia = j; }
+      mb2 = fminf(mb2, fmaxf(sb, mb1));
+      if (sb < mb1) { mb1 = sb; ib = j + 1; }
     }
   }
+  // merge the trackers; on equal scores the smaller index wins
+  float m1, m2;
+  int i1;
+  if (mb1 < ma1 || (mb1 == ma1 && ib < ia)) { m1 = mb1; i1 = ib; m2 = fminf(ma1, mb2); }
+  else { m1 = ma1; i1 = ia; m2 = fminf(mb1, ma2); }
   s.pmin[half][r] = m1; s.pmin2[half][r] = m2; s.pidx[half][r] = i1;
   __syncthreads();
   bool amb = false;
@@ -253,7 +274,10 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
     float best = m1, second = fminf(m2, n1);
     int bi = i1;
     if (n1 < m1) { best = n1; bi = k1; second = fminf(m1, n2); }
-    const float band = 2.f * kBand * sqrtf(s.sx2[r]) * s.cmax + 4e-7f * fabsf(best);
+    float cmax = s.cmax_w[0];
+#pragma unroll
+    for (int i = 1; i < kThreads / 32; ++i) cmax = fmaxf(cmax, s.cmax_w[i]);
+    const float band = 2.f * kBand * sqrtf(s.sx2[r]) * cmax + 4e-7f * fabsf(best);
     s.rmin[r] = best; s.band[r] = band;
     amb = (r < nrows) && (second - best <= band);
     s.ambiguous[r] = amb ? 1 : 0;
@@ -384,11 +408,13 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   const size_t smem = sizeof(PqSmem) + 1024;
   static bool attr_done[64] = {};
   if (!attr_done[dev & 63]) {
-    PT_CUDA(cudaFuncSetAttribute(pq_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PT_CUDA(cudaFuncSetAttribute(pq_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PT_CUDA(cudaFuncSetAttribute(pq_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done[dev & 63] = true;
   }
   dim3 grid((unsigned)((rows + a.rows_per_tile - 1) / a.rows_per_tile), (unsigned)G);
-  pq_search_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
+  if (score_dump) pq_search_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
+  else pq_search_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
   PT_CUDA(cudaGetLastError());
   return 0;
 }

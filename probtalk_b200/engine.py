@@ -48,9 +48,10 @@ def _bn_scale_shift(sd, prefix, eps=1e-5):
 class Weight:
     """bf16 [Npad, taps*Cp] matrix + fp32 bias [Npad] on the device."""
 
-    def __init__(self, mat, bias, taps, Cp, n_valid):
+    def __init__(self, mat, bias, taps, Cp, n_valid, cin=None):
         self.mat, self.bias, self.taps, self.Cp, self.n_valid = mat, bias, taps, Cp, n_valid
         self.N = mat.shape[0]
+        self.cin = cin if cin is not None else Cp       # true (unpadded) input channels per tap
 
 
 def _finish(wm, bias, taps, Cp, device):
@@ -62,7 +63,7 @@ def _finish(wm, bias, taps, Cp, device):
     b = torch.zeros(Npad, dtype=F32, device=wm.device)
     if bias is not None:
         b[:N] = bias
-    return Weight(full.reshape(Npad, taps * Cp).to(device=device, dtype=BF16).contiguous(), b.to(device), taps, Cp, N)
+    return Weight(full.reshape(Npad, taps * Cp).to(device=device, dtype=BF16).contiguous(), b.to(device), taps, Cp, N, Cin)
 
 
 def prep_conv(w, b, device, bn=None, extra=None, gate=False, cin_pad=None):
@@ -141,24 +142,28 @@ class Plan:
         self.launches = 0
 
     # -- generic recorders
-    def call(self, fn, *args):
-        self.steps.append((fn, args))
+    def call(self, fn, *args, flops=0.0):
+        self.steps.append((fn, args, flops))
         self.launches += 1
 
     def run(self):
         st = _stream()
-        L = _lib.lib()
-        for fn, args in self.steps:
-            if fn is None:
-                args[0]()
-                continue
+        for fn, args, _ in self.steps:
             rc = fn(*args, st)
             if rc != 0:
                 check(rc, fn.__name__)
 
-    def host(self, f):
-        """A host-side callback between launches (e.g. drawing sampler noise with torch)."""
-        self.steps.append((None, (f,)))
+    def run_timed(self, records):
+        """Replay with a CUDA event pair around every launch; appends (name, start, end, flops) to records."""
+        st = _stream()
+        for fn, args, flops in self.steps:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*args, st)
+            if rc != 0:
+                check(rc, fn.__name__)
+            e1.record()
+            records.append((fn.__name__, e0, e1, flops))
 
     # -- GEMM recorders
     def gemm(self, a_t, a_rows, a_pitch, w: Weight, out_t, *, M, C_, s=1, base_row=0, rows_per_sample, t_valid,
@@ -184,7 +189,9 @@ class Plan:
         d.rss, d.rrs = rss, rrs
         d.act, d.slope = act, slope
         self.keep += [a_t, w, out_t, residual, d]
-        self.call(_lib.lib().pt_gemm_bf16, C.byref(d))
+        # algorithmic FLOPs: real output rows x real output channels x real input channels (no padding / halo credit)
+        flops = 2.0 * M * (t_valid / float(rows_per_sample)) * d.n_valid * w.taps * w.cin
+        self.call(_lib.lib().pt_gemm_bf16, C.byref(d), flops=flops)
 
     def conv(self, x: RowBuf, w: Weight, out: RowBuf, *, k, stride=1, pad=None, act=ACT_NONE, slope=0.2,
              residual: RowBuf = None, out_c_off=0):
@@ -290,13 +297,16 @@ class EncoderPlan:
                x0.C, 0, 0)
         h = RowBuf(B, T, 256, 1, device=dev)
         p.conv(x0, W.enc_project, h, k=3, act=ACT_LEAKY)
+        self.stages = [("project", h)]
         chans = [256, 512, 1024]
         for i in range(4):
             h = _stack_steps(p, h, W.enc_stacks[i], B, dev)
+            self.stages.append(("_enc_%d" % (i + 1), h))
             if i < 3:
                 d = RowBuf(B, (h.T - 2) // 2 + 1, chans[i], 1, device=dev)
                 p.conv(h, W.enc_downs[i], d, k=4, stride=2, pad=1, act=ACT_LEAKY)
                 h = d
+                self.stages.append(("_down_%d" % (i + 1), h))
         self.Tq = h.T
         self.z = RowBuf(B, h.T, 512, 0, dtype=F32, device=dev)
         p.conv(h, W.pre_vq, self.z, k=1)
@@ -320,25 +330,34 @@ class DecoderPlan:
     """quantize_all + DecoderSC.forward (vqvae_modules.py:557-564, vqvae_1d_sc.py:259-274).
     codes [B, T', G] -> poses fp32 [B, 376, 8 T'] (channel-first, the reference layout)."""
 
-    def __init__(self, W: VQVAEWeights, B, Tq, codes=None):
+    def __init__(self, W: VQVAEWeights, B, Tq, codes=None, from_latents=False):
         dev = W.device
         self.W, self.B, self.Tq = W, B, Tq
         p = self.plan = Plan(dev)
         L = _lib.lib()
-        self.codes = codes if codes is not None else torch.zeros(B, Tq, W.groups, dtype=torch.int64, device=dev)
         self.bad = torch.zeros(1, dtype=torch.int32, device=dev)
         e = RowBuf(B, Tq, 512, 0, device=dev)
-        p.call(L.pt_pq_gather, self.codes.data_ptr(), int(self.codes.dtype == torch.int64), W.codebooks.data_ptr(),
-               e.t.data_ptr(), 1, e.Tp * 512, 1, 512, B, Tq, W.groups, 128, 128, self.bad.data_ptr())
+        if from_latents:
+            # VQ.decode(latents, None) on arbitrary [B, 512, T'] fp32 latents (scripts/demo.py:152-153)
+            self.codes = None
+            self.latents = torch.zeros(B, 512, Tq, dtype=F32, device=dev)
+            p.call(L.pt_pack_rows, self.latents.data_ptr(), None, None, 0, e.t.data_ptr(), B, 512, Tq, e.Tp, 0, 512, 0, 0)
+        else:
+            self.codes = codes if codes is not None else torch.zeros(B, Tq, W.groups, dtype=torch.int64, device=dev)
+            p.call(L.pt_pq_gather, self.codes.data_ptr(), int(self.codes.dtype == torch.int64), W.codebooks.data_ptr(),
+                   e.t.data_ptr(), 1, e.Tp * 512, 1, 512, B, Tq, W.groups, 128, 128, self.bad.data_ptr())
         h = RowBuf(B, Tq, 1024, 1, device=dev)
         p.conv(e, W.aft_vq, h, k=1)
+        self.stages = [("aft_vq_conv", h)]
         chans = [512, 256, 256]
         for i in range(4):
             h = _stack_steps(p, h, W.dec_stacks[i], B, dev)
+            self.stages.append(("_dec_%d" % (i + 1), h))
             if i < 3:
                 u = RowBuf(B, 2 * h.T, chans[i], 1, device=dev)
                 p.convT(h, W.dec_ups[i], u, act=ACT_LEAKY)
                 h = u
+                self.stages.append(("_up_%d" % (i + 2), h))
         self.T_out = h.T
         self.out = torch.zeros(B, W.in_dim, self.T_out, dtype=F32, device=dev)
         w = W.dec_project
@@ -346,8 +365,392 @@ class DecoderPlan:
                oss=W.in_dim * self.T_out, ors=1, ocs=self.T_out)
         p.keep += [e]
 
-    def run(self, codes=None):
+    def run(self, codes=None, latents=None):
         if codes is not None:
             self.codes.copy_(codes)
+        if latents is not None:
+            self.latents.copy_(latents)
+        self.plan.run()
+        return self.out
+
+
+# ----------------------------------------------------------------------------------------------
+# transformer decoder stack shared by predictor and refiner
+# (reference: DeepSupervisionLayer / StylizationBlock_V3, nets/inpainting/PTransformer.py:28-165, :284-372)
+# ----------------------------------------------------------------------------------------------
+
+D_MODEL, N_HEADS, HEAD_DIM = 512, 8, 64
+
+
+class StyleWeights:
+    """One StylizationBlock_V3 ('sb'): LN affine, per-class [scale | shift] table, output Linear."""
+
+    def __init__(self, sd, p, class_embed, device):
+        self.gamma = sd[p + ".norm_2.weight"].float().to(device).contiguous()
+        self.beta = sd[p + ".norm_2.bias"].float().to(device).contiguous()
+        w, b = sd[p + ".emb_layers_2.1.weight"].float().to(device), sd[p + ".emb_layers_2.1.bias"].float().to(device)
+        # emb_layers_2 = Linear(SiLU(class_embed[label])) depends on the label only: tabulate it per class (fp32)
+        self.mod = torch.nn.functional.linear(torch.nn.functional.silu(class_embed), w, b).contiguous()   # [n_classes, 1024]
+        self.out = prep_linear(sd[p + ".out_layers_2.2.weight"], sd[p + ".out_layers_2.2.bias"], device)
+
+
+class LayerWeights:
+    def __init__(self, sd, p, class_embed, device):
+        C_ = D_MODEL
+        Wi, bi = sd[p + ".self_attn.in_proj_weight"], sd[p + ".self_attn.in_proj_bias"]
+        self.qkv = prep_linear(Wi, bi, device)
+        self.sa_out = prep_linear(sd[p + ".self_attn.out_proj.weight"], sd[p + ".self_attn.out_proj.bias"], device)
+        Wc, bc = sd[p + ".multihead_attn.in_proj_weight"], sd[p + ".multihead_attn.in_proj_bias"]
+        self.ca_q = prep_linear(Wc[:C_], bc[:C_], device)
+        self.ca_kv_w, self.ca_kv_b = Wc[C_:], bc[C_:]          # stacked across layers by the stack builder
+        self.ca_out = prep_linear(sd[p + ".multihead_attn.out_proj.weight"], sd[p + ".multihead_attn.out_proj.bias"], device)
+        self.ff1 = prep_linear(sd[p + ".linear1.weight"], sd[p + ".linear1.bias"], device)
+        self.ff2 = prep_linear(sd[p + ".linear2.weight"], sd[p + ".linear2.bias"], device)
+        self.norms = [(sd[p + ".norm%d.weight" % i].float().to(device).contiguous(),
+                       sd[p + ".norm%d.bias" % i].float().to(device).contiguous()) for i in (1, 2, 3)]
+        self.styles = [StyleWeights(sd, p + ".style_gourp_%d" % i, class_embed, device) for i in (1, 2, 3)]
+
+
+class StackWeights:
+    def __init__(self, sd, prefix, class_embed, device, n_layers=6):
+        self.layers = [LayerWeights(sd, "%s.layers.%d" % (prefix, l), class_embed, device) for l in range(n_layers)]
+        # cross-attention K/V projections of all layers as ONE GEMM over the (constant) memory
+        w = torch.cat([lw.ca_kv_w for lw in self.layers], 0)
+        b = torch.cat([lw.ca_kv_b for lw in self.layers], 0)
+        self.kv_all = prep_linear(w, b, device)
+
+
+class StackPlanner:
+    """Records the launches of a 6-layer DeepSupervisionLayer stack over fixed buffers.
+
+    x32 / xb : fp32 master + bf16 copy of the residual stream [B*N, 512]
+    memb     : bf16 memory rows [B*Mem, 512]; labels int32 [B]."""
+
+    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device):
+        self.p, self.W, self.B, self.N, self.Mem = plan, W, B, N, Mem
+        M = B * N
+        self.M = M
+        z = lambda *s, dt=BF16: torch.zeros(*s, dtype=dt, device=device)
+        self.x32, self.xb = z(M, D_MODEL, dt=F32), z(M, D_MODEL)
+        self.memb = z(B * Mem, D_MODEL)
+        self.kv = z(B * Mem, 2 * D_MODEL * len(W.layers))
+        self.qkv = z(M, 3 * D_MODEL)
+        self.q = z(M, D_MODEL)
+        self.att = z(M, D_MODEL)
+        self.proj = z(M, D_MODEL)
+        self.sil = z(M, D_MODEL)
+        self.r32 = z(M, D_MODEL, dt=F32)
+        self.ff = z(M, 4 * D_MODEL)
+        self.labels = labels
+
+    def record_memory_kv(self):
+        self.p.linear(self.memb, self.B * self.Mem, self.W.kv_all, self.kv)
+
+    def _style_residual_norm(self, lw: LayerWeights, i):
+        """x = norm_i( x + style_i(proj) )   (PTransformer.py:329-331 with :134-140)."""
+        L = _lib.lib()
+        st = lw.styles[i]
+        p, M = self.p, self.M
+        p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
+               self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
+        p.linear(self.sil, M, st.out, self.r32, residual=self.x32, rss=0, rrs=D_MODEL, rows_per_sample=None)
+        g, b = lw.norms[i]
+        p.call(L.pt_layernorm512, self.r32.data_ptr(), g.data_ptr(), b.data_ptr(), self.x32.data_ptr(), self.xb.data_ptr(), M)
+
+    def record_layers(self):
+        L = _lib.lib()
+        p, M, B, N, Mem = self.p, self.M, self.B, self.N, self.Mem
+        scale = 1.0 / math.sqrt(HEAD_DIM)
+        nl = len(self.W.layers)
+        for l, lw in enumerate(self.W.layers):
+            # self attention
+            p.linear(self.xb, M, lw.qkv, self.qkv)
+            p.call(L.pt_attention, self.qkv.data_ptr(), 3 * D_MODEL, self.qkv.data_ptr() + 2 * D_MODEL, 3 * D_MODEL,
+                   self.qkv.data_ptr() + 4 * D_MODEL, 3 * D_MODEL, self.att.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM,
+                   N, N, scale)
+            p.linear(self.att, M, lw.sa_out, self.proj)
+            self._style_residual_norm(lw, 0)
+            # cross attention over the memory
+            p.linear(self.xb, M, lw.ca_q, self.q)
+            kv_stride = 2 * D_MODEL * nl
+            kptr = self.kv.data_ptr() + 2 * (l * 2 * D_MODEL)
+            p.call(L.pt_attention, self.q.data_ptr(), D_MODEL, kptr, kv_stride, kptr + 2 * D_MODEL, kv_stride,
+                   self.att.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM, N, Mem, scale)
+            p.linear(self.att, M, lw.ca_out, self.proj)
+            self._style_residual_norm(lw, 1)
+            # feed forward
+            p.linear(self.xb, M, lw.ff1, self.ff, act=ACT_RELU)
+            p.linear(self.ff, M, lw.ff2, self.proj)
+            self._style_residual_norm(lw, 2)
+
+
+# ----------------------------------------------------------------------------------------------
+# predictor  (reference: predictor.TrainWrapper.infer_on_batch / infer_to_code,
+#             nets/inpainting/predictor.py:398-448, :597-647; PredictorNet.forward predictornet.py:76-112;
+#             PTransformer.sample_good / tokens_to_logits, PTransformer.py:590-704)
+# ----------------------------------------------------------------------------------------------
+
+MASK_ID = 128
+CHOICE_TEMPERATURE = 4.5
+
+
+class PredictorWeights:
+    def __init__(self, state, device):
+        dev = device
+        aud = {k: v.to(dev) for k, v in state["AudEnc"].items() if torch.is_tensor(v)}
+        sd = {k: v.to(dev) for k, v in state["Predictor"].items() if torch.is_tensor(v)}
+        self.device = dev
+        # AudEnc (ConditionEncoder, vqvae_1d_sc.py:70-91)
+        self.aud_map = prep_conv(aud["feature_map.0.weight"], aud["feature_map.0.bias"], dev,
+                                 bn=_bn_scale_shift(aud, "feature_map.1"))
+        self.aud_downs = [prep_conv(aud["_down_%d.conv.weight" % i], aud["_down_%d.conv.bias" % i], dev,
+                                    bn=_bn_scale_shift(aud, "_down_%d.norm" % i),
+                                    extra=(aud["_down_%d.residual_layer.weight" % i], aud["_down_%d.residual_layer.bias" % i]))
+                          for i in (1, 2, 3)]
+        # context encoder (predictornet.py:31-48, gated_pixelcnn_1d.py:39-83)
+        self.mot_dim = sd["motion_embedding.weight"].shape[1] - 1
+        self.embed = prep_conv(sd["motion_embedding.weight"], sd["motion_embedding.bias"], dev)
+        self.enc = []
+        for i in range(10):
+            p = "enc.%d" % i
+            k = sd[p + ".vert_stack.weight"].shape[2]
+            stride = 2 if (p + ".conv.weight") in sd else 1
+            item = dict(k=k, stride=stride, pad=3 if k == 7 else 1,
+                        cin=sd[p + ".vert_stack.weight"].shape[1], dim=sd[p + ".res.weight"].shape[0],
+                        vert=prep_conv(sd[p + ".vert_stack.weight"], sd[p + ".vert_stack.bias"], dev, gate=True),
+                        res=prep_linear(sd[p + ".res.weight"], sd[p + ".res.bias"], dev))
+            if stride == 2:
+                item["skip"] = prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev)
+            self.enc.append(item)
+        # PTransformer
+        d = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
+        self.tok_emb = d["tok_emb.weight"].float().contiguous()
+        self.n_emb = self.tok_emb.shape[0]
+        self.class_embed = d["class_embed.weight"].float()
+        self.PE = d["PE.position_encoding.weight"].double()
+        self.PPE = d["product_PE.position_encoding.weight"].double()
+        self.groups = self.PPE.shape[0] - 1
+        self.condi = prep_linear(d["condi_emb.weight"], d["condi_emb.bias"], dev)
+        self.stack = StackWeights(d, "transformer_decoder", self.class_embed, dev)
+        self.head0 = prep_linear(d["output_conv.0.weight"], d["output_conv.0.bias"], dev)
+        self.head1 = prep_linear(d["output_conv.2.weight"], d["output_conv.2.bias"], dev)
+        self.n_codes = d["output_conv.2.weight"].shape[0]
+
+
+def maskgit_base_len(N, step, T):
+    """floor(N * cos(pi/2 * (step+1)/T)) evaluated like the reference: int64 tensor * numpy float64 -> float32
+    (PTransformer.py:610-621)."""
+    ratio = 1.0 * (step + 1) / T
+    mask_ratio = np.cos(ratio * np.pi / 2)
+    return int(torch.floor(torch.tensor([N], dtype=torch.int64) * mask_ratio).item())
+
+
+class PredictorPlan:
+    """One (B, T) bucket of s2g_body_predictor inference on already-batched inputs:
+         aud [B,768,T], gt_poses [B,376,T], mask [B,1,T], labels [B]  ->  poses [B,376,T], codes [B,T',G]."""
+
+    def __init__(self, PW: PredictorWeights, VW: VQVAEWeights, B, T, maskgit_T=8):
+        dev = PW.device
+        self.PW, self.VW, self.B, self.T, self.steps_T = PW, VW, B, T, maskgit_T
+        L = _lib.lib()
+        G = PW.groups
+        f32 = lambda *s: torch.zeros(*s, dtype=F32, device=dev)
+        self.aud, self.gt, self.mask = f32(B, 768, T), f32(B, PW.mot_dim, T), f32(B, 1, T)
+        self.labels = torch.zeros(B, dtype=torch.int32, device=dev)
+        # ---------------- plan A: condition (AudEnc + context encoder + memory K/V) ----------------
+        pa = self.plan_cond = Plan(dev)
+        xa = RowBuf(B, T, 768, 0, device=dev)
+        pa.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xa.t.data_ptr(), B, 768, T, xa.Tp, xa.H, xa.C, 0, 0)
+        h = RowBuf(B, T, 256, 1, device=dev)
+        pa.conv(xa, PW.aud_map, h, k=1, act=ACT_LEAKY, slope=0.1)
+        Tq = T
+        for i in range(3):
+            Tq = (Tq - 2) // 2 + 1
+        self.Tq = Tq
+        self.N = Tq * G
+        cond = RowBuf(B, Tq, 768, 0, device=dev)                   # [mm (512) | audio (256)]  (predictornet.py:93-95)
+        for i in range(3):
+            To = (h.T - 2) // 2 + 1
+            if i < 2:
+                d = RowBuf(B, To, 256, 1, device=dev)
+                pa.conv(h, PW.aud_downs[i], d, k=4, stride=2, pad=1, act=ACT_LEAKY)
+                h = d
+            else:
+                pa.conv(h, PW.aud_downs[i], cond, k=4, stride=2, pad=1, act=ACT_LEAKY, out_c_off=512)
+        xm = RowBuf(B, T, _ceil(PW.mot_dim + 1, 64), 0, device=dev)
+        pa.call(L.pt_pack_rows, self.gt.data_ptr(), self.mask.data_ptr(), None, 0, xm.t.data_ptr(), B, PW.mot_dim, T,
+                xm.Tp, xm.H, xm.C, 0, 1)
+        pa.call(L.pt_pack_mask, self.mask.data_ptr(), xm.t.data_ptr(), B, T, xm.Tp, xm.H, xm.C, PW.mot_dim, 0)
+        mm = RowBuf(B, T, 128, 3, device=dev)
+        pa.conv(xm, PW.embed, mm, k=1)
+        self.ctx_stages = [("motion_embedding", mm)]
+        for i, e in enumerate(PW.enc):
+            To = mm.T if e["stride"] == 1 else (mm.T - 2) // 2 + 1
+            gate = RowBuf(B, To, e["dim"], 0, device=dev)
+            pa.conv(mm, e["vert"], gate, k=e["k"], stride=e["stride"], pad=e["pad"], act=ACT_GATE)
+            if e["stride"] == 2:
+                skip = RowBuf(B, To, e["dim"], 0, device=dev)
+                pa.conv(mm, e["skip"], skip, k=4, stride=2, pad=1)
+            else:
+                skip = mm
+            last = i == len(PW.enc) - 1
+            if last:
+                pa.conv(gate, e["res"], cond, k=1, residual=skip, out_c_off=0)
+                nxt = cond
+            else:
+                nxt = RowBuf(B, To, e["dim"], 1, device=dev)
+                pa.conv(gate, e["res"], nxt, k=1, residual=skip)
+            mm = nxt
+            self.ctx_stages.append(("enc.%d" % i, mm))
+        assert mm.T == Tq
+        self.cond = cond
+        # positional tables (PTransformer.py:669-674): token (t, g) -> PE[t+1] + product_PE[g+1]; memory t -> PE[t+1]
+        c_pe = PW.PE[1:Tq + 1]
+        x_pe = c_pe.repeat_interleave(G, 0) + PW.PPE[1:G + 1].repeat(Tq, 1)
+        self.x_pe64 = x_pe.contiguous().to(dev)
+        self.c_pe32 = c_pe.float().contiguous().to(dev)
+        self.stack = StackPlanner(pa, PW.stack, B, self.N, Tq, self.labels, dev)
+        # condition embedding 1x1 (768 -> 512) + PE, rounded once to bf16 (only ever a GEMM operand)
+        pa.gemm(cond.t, B * cond.Tp, 768, PW.condi, self.stack.memb, M=B * cond.Tp, C_=768, base_row=0,
+                rows_per_sample=cond.Tp, t_valid=Tq, oss=Tq * D_MODEL, ors=D_MODEL, residual=self.c_pe32, rss=0,
+                rrs=D_MODEL)
+        self.stack.record_memory_kv()
+        # ---------------- plan B: one MaskGIT iteration (embed -> 6 layers -> logits) ----------------
+        pb = self.plan_iter = Plan(dev)
+        self.stack.p = pb
+        M = B * self.N
+        self.cur = torch.full((B, self.N), MASK_ID, dtype=torch.int32, device=dev)
+        self.bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        pb.call(L.pt_embed_tokens512, self.cur.data_ptr(), PW.tok_emb.data_ptr(), PW.n_emb, self.x_pe64.data_ptr(), self.N,
+                self.stack.x32.data_ptr(), self.stack.xb.data_ptr(), M, self.bad.data_ptr())
+        self.stack.record_layers()
+        self.h1 = torch.zeros(M, D_MODEL, dtype=BF16, device=dev)
+        self.logits = torch.zeros(M, PW.n_codes, dtype=F32, device=dev)
+        pb.linear(self.stack.xb, M, PW.head0, self.h1, act=ACT_RELU)
+        pb.linear(self.h1, M, PW.head1, self.logits)
+        # ---------------- sampler steps (one tiny plan per MaskGIT iteration) ----------------
+        self.u = f32(maskgit_T, B, self.N)
+        self.gumbel = f32(maskgit_T, B, self.N)
+        self.base_len = [maskgit_base_len(self.N, t, maskgit_T) for t in range(maskgit_T)]
+        self.plan_sample = []
+        for t in range(maskgit_T):
+            ps = Plan(dev)
+            ratio = 1.0 * (t + 1) / maskgit_T
+            ps.call(L.pt_maskgit_step, self.logits.data_ptr(), self.cur.data_ptr(), self.u[t].data_ptr(),
+                    self.gumbel[t].data_ptr(), self.cur.data_ptr(), B, self.N, PW.n_codes, MASK_ID, self.base_len[t],
+                    CHOICE_TEMPERATURE * (1.0 - ratio))
+            self.plan_sample.append(ps)
+        # ---------------- plan C: decode (the token buffer IS the [B, T', G] int32 code tensor) ----------------
+        self.codes = self.cur.view(B, Tq, G)
+        self.dec = DecoderPlan(VW, B, Tq, codes=self.codes)
+        self.out = f32(B, PW.mot_dim, T)
+        self.dec.plan.call(L.pt_interp_blend, self.gt.data_ptr(), self.mask.data_ptr(), self.dec.out.data_ptr(), self.dec.T_out,
+                           self.out.data_ptr(), B, PW.mot_dim, T, 2)
+        self.launches = pa.launches + maskgit_T * (pb.launches + 1) + self.dec.plan.launches
+
+    def plans_in_order(self):
+        seq = [self.plan_cond]
+        for t in range(self.steps_T):
+            seq += [self.plan_iter, self.plan_sample[t]]
+        return seq + [self.dec.plan]
+
+    def draw_noise(self, generator=None):
+        """Sampler noise on the device: u ~ U(0,1) for the categorical draw, Gumbel(0,1) for the confidences."""
+        self.u.uniform_(generator=generator)
+        g = torch.empty_like(self.gumbel).uniform_(generator=generator).clamp_(1e-10, 1 - 1e-7)
+        self.gumbel.copy_(-torch.log(-torch.log(g)))
+
+    def run_condition(self):
+        self.plan_cond.run()
+
+    def run_iteration(self, t):
+        """tokens_to_logits + one sample_good step (PTransformer.py:603-638) using noise slice t."""
+        self.plan_iter.run()
+        self.plan_sample[t].run()
+
+    def run_decode(self):
+        self.dec.plan.run()
+        return self.out
+
+    def run(self, aud, gt, mask, labels, noise=None, generator=None):
+        """Full infer_to_code for a batch.  noise = (u, gumbel) [T, B, N] to inject, else drawn on the device.
+        Returns (poses [B,376,T] fp32, codes [B,T',G] int32) -- views of plan-owned buffers."""
+        self.aud.copy_(aud); self.gt.copy_(gt); self.mask.copy_(mask); self.labels.copy_(labels)
+        if noise is not None:
+            self.u.copy_(noise[0]); self.gumbel.copy_(noise[1])
+        else:
+            self.draw_noise(generator)
+        self.cur.fill_(MASK_ID)
+        for pl in self.plans_in_order():
+            pl.run()
+        return self.out, self.codes
+
+
+# ----------------------------------------------------------------------------------------------
+# refiner  (reference: refiner.TrainWrapper.infer_on_batch, nets/inpainting/refiner.py:512-558;
+#           RTransformer.forward, nets/inpainting/RTransformer.py:209-230)
+# ----------------------------------------------------------------------------------------------
+
+class RefinerWeights:
+    def __init__(self, state, device):
+        dev = device
+        sd = {k: v.to(dev) for k, v in state["HFTransformer"].items() if torch.is_tensor(v)}
+        self.device = dev
+        self.in_dim = sd["input_conv.weight"].shape[1]
+        self.aud_dim = sd["audio_conv.weight"].shape[1] - 2
+        self.class_embed = sd["class_embed.weight"].float()
+        self.PE = sd["PE.position_encoding.weight"].double()
+        self.input_conv = prep_linear(sd["input_conv.weight"], sd["input_conv.bias"], dev)
+        self.audio_conv = prep_linear(sd["audio_conv.weight"], sd["audio_conv.bias"], dev)
+        self.stack = StackWeights(sd, "transformer_decoder", self.class_embed, dev)
+        self.head0 = prep_linear(sd["output_conv.0.weight"], sd["output_conv.0.bias"], dev)
+        self.head1 = prep_linear(sd["output_conv.2.weight"], sd["output_conv.2.bias"], dev)
+
+
+class RefinerPlan:
+    """One (B, T) bucket: aud [B,768,T], gt [B,376,T], mask [B,1,T], pred [B,376,Tpred], labels [B] -> [B,376,T]."""
+
+    def __init__(self, RW: RefinerWeights, B, T, T_pred=None):
+        dev = RW.device
+        self.RW, self.B, self.T = RW, B, T
+        self.T_pred = T_pred or T
+        L = _lib.lib()
+        f32 = lambda *s: torch.zeros(*s, dtype=F32, device=dev)
+        self.aud, self.gt, self.mask = f32(B, RW.aud_dim, T), f32(B, RW.in_dim, T), f32(B, 1, T)
+        self.pred = f32(B, RW.in_dim, self.T_pred)
+        self.labels = torch.zeros(B, dtype=torch.int32, device=dev)
+        p = self.plan = Plan(dev)
+        M = B * T
+        # blank = gt*mask + interp(pred)*(1-mask)  -> rows [B*T, 384]
+        xin = RowBuf(B, T, _ceil(RW.in_dim, 64), 0, device=dev)
+        assert xin.Tp == T, "refiner windows must have an even number of frames"
+        p.call(L.pt_pack_rows, self.gt.data_ptr(), self.mask.data_ptr(), self.pred.data_ptr(), self.T_pred, xin.t.data_ptr(),
+               B, RW.in_dim, T, xin.Tp, 0, xin.C, 0, 2)
+        # condition = cat(audio, one_hot(mask))  -> rows [B*T, 832]
+        xc = RowBuf(B, T, _ceil(RW.aud_dim + 2, 64), 0, device=dev)
+        p.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xc.t.data_ptr(), B, RW.aud_dim, T, xc.Tp, 0, xc.C, 0, 0)
+        p.call(L.pt_pack_mask, self.mask.data_ptr(), xc.t.data_ptr(), B, T, xc.Tp, 0, xc.C, RW.aud_dim, 1)
+        self.pe32 = RW.PE[1:T + 1].float().contiguous().to(dev)
+        self.stack = StackPlanner(p, RW.stack, B, T, T, self.labels, dev)
+        st = self.stack
+        # x = float32(input_conv(blank) + PE)   (RTransformer.py:211-214)
+        p.linear(xin.t, M, RW.input_conv, st.x32, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
+        p.linear(xin.t, M, RW.input_conv, st.xb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
+        p.linear(xc.t, M, RW.audio_conv, st.memb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
+        st.record_memory_kv()
+        st.record_layers()
+        self.h1 = torch.zeros(M, 1024, dtype=BF16, device=dev)
+        self.raw = f32(B, RW.in_dim, T)
+        p.linear(st.xb, M, RW.head0, self.h1, act=ACT_RELU)
+        w = RW.head1
+        p.gemm(self.h1, M, 1024, w, self.raw, M=M, C_=1024, rows_per_sample=T, t_valid=T, oss=RW.in_dim * T, ors=1, ocs=T)
+        self.out = f32(B, RW.in_dim, T)
+        p.call(L.pt_interp_blend, self.gt.data_ptr(), self.mask.data_ptr(), self.raw.data_ptr(), T, self.out.data_ptr(), B,
+               RW.in_dim, T, 1)
+        self.launches = p.launches
+        p.keep += [xin, xc]
+
+    def run(self, aud, gt, mask, pred, labels):
+        self.aud.copy_(aud); self.gt.copy_(gt); self.mask.copy_(mask); self.pred.copy_(pred); self.labels.copy_(labels)
         self.plan.run()
         return self.out

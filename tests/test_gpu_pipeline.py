@@ -1,0 +1,290 @@
+"""PQ-VAE / predictor / refiner CUDA plans vs the oracle and the reference-generated golden vectors.
+
+Arithmetic type: bf16 tensor-core operands, fp32 accumulation, bf16 activations between layers (the reference
+is fp32).  Stated tolerances (normalised pose units, decoder output rms ~0.5, refiner output rms ~0.9):
+    PQ-VAE decode from identical codes      max-abs <= 0.04   mean-abs <= 0.006    (observed 0.012 / 0.002)
+    predictor poses from identical codes    max-abs <= 0.04                        (observed 0.011)
+    teacher-forced logits                   max-abs <= 0.12   rms <= 0.02          (observed 0.035 / 0.007)
+    refiner output                          max-abs <= 0.08   mean-abs <= 0.012    (observed 0.022 / 0.003)
+    per-joint (6-D block) mean error        <= 0.02
+PQ codes emitted from the CUDA encoder's own z are index-exact w.r.t. that z; against the fp32 reference's codes
+they may differ where the bf16 encoder error exceeds the top-2 gap (reported, bounded below)."""
+import os
+
+import pytest
+import torch
+
+from oracle import probtalk_oracle as O
+from probtalk_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.pt")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return torch.load(GOLD, map_location="cpu", weights_only=False)
+
+
+@pytest.fixture(scope="module")
+def states(gold):
+    s = gold["seeds"]
+    return S.make_vq_state(s["vq"]), S.make_predictor_state(s["pred"]), S.make_refiner_state(s["ref"])
+
+
+@pytest.fixture(scope="module")
+def weights(states):
+    from probtalk_b200 import engine as E
+    return E.VQVAEWeights(states[0], "cuda"), E.PredictorWeights(states[1], "cuda"), E.RefinerWeights(states[2], "cuda")
+
+
+def noise(T, B, N, seed):
+    g = torch.Generator().manual_seed(seed)
+    u = torch.rand(T, B, N, generator=g)
+    gum = -torch.log(-torch.log(torch.rand(T, B, N, generator=g).clamp_(1e-10, 1 - 1e-7)))
+    return u, gum
+
+
+def per_joint_error(a, b):
+    """mean over joints of the L2 error of each 6-D rotation block (46 joints = jaw + 15 body + 30 hands)."""
+    d = (a - b)[:, :276].reshape(a.shape[0], 46, 6, -1)
+    return d.pow(2).sum(2).sqrt().mean().item()
+
+
+def test_cfg1_vqvae_golden(gold, states, weights):
+    """BASELINE config 1: one 300-frame clip, encode -> PQ -> decode, against the reference's own output."""
+    from probtalk_b200 import engine as E
+    c = gold["cfg1"]
+    x = S.synthetic_poses(1, 300, c["poses_seed"])
+    enc = E.EncoderPlan(weights[0], 1, 300)
+    codes = enc.run(x.cuda()).cpu()
+    z = enc.z_channel_first().cpu()
+    assert z.shape == c["z"].shape
+    assert (z - c["z"]).abs().max() < 0.2 and (z - c["z"]).pow(2).mean().sqrt() < 0.03
+    # index-exact with respect to the z the encoder produced
+    cbs = O.pq_codebooks(states[0])
+    self_ref = O.pq_search(z, cbs)
+    _, gap = O.pq_search_fp64(z, cbs)
+    bad = codes != self_ref
+    assert bool((gap[bad] < O.pq_tie_eps(z, cbs)[bad]).all())
+    # versus the fp32 reference codes: only where the encoder's bf16 error can flip the winner
+    ref_codes = c["codes"].long()
+    diff = codes != ref_codes
+    _, gap_ref = O.pq_search_fp64(c["z"], cbs)
+    dz = (z - c["z"]).permute(0, 2, 1).reshape(1, -1, 4, 128).norm(dim=-1)          # per (step, group) |dz|
+    cmax = max(cb.norm(dim=1).max().item() for cb in cbs)
+    assert bool((gap_ref[diff] <= 4.0 * dz[diff] * cmax + 1e-4).all())
+    assert diff.float().mean() < 0.1
+    # decode the REFERENCE codes: tolerance-matched poses
+    rec = E.DecoderPlan(weights[0], 1, enc.Tq).run(codes=ref_codes.cuda()).cpu()
+    assert rec.shape == c["recon"].shape == (1, 376, 296)
+    err = (rec - c["recon"]).abs()
+    assert err.max() < 0.04 and err.mean() < 0.006
+    assert per_joint_error(rec, c["recon"]) < 0.02
+
+
+@pytest.mark.parametrize("B,T", [(3, 180), (2, 150), (1, 64), (5, 301)])
+def test_vqvae_shapes_vs_oracle(states, weights, B, T):
+    """Ragged lengths (odd T, T not a multiple of 8) through encoder and decoder."""
+    from probtalk_b200 import engine as E
+    x = S.synthetic_poses(B, T, 77 + T)
+    z_ref, idx_ref, rec_ref = O.vqvae_forward(x, states[0])
+    enc = E.EncoderPlan(weights[0], B, T)
+    codes = enc.run(x.cuda()).cpu()
+    assert codes.shape == idx_ref.shape
+    z = enc.z_channel_first().cpu()
+    assert (z - z_ref).abs().max() < 0.25
+    assert (codes == idx_ref).float().mean() > 0.85
+    rec = E.DecoderPlan(weights[0], B, enc.Tq).run(codes=idx_ref.cuda()).cpu()
+    assert rec.shape == rec_ref.shape
+    assert (rec - rec_ref).abs().max() < 0.04
+
+
+def test_decode_from_latents_matches_decode_from_codes(states, weights):
+    from probtalk_b200 import engine as E
+    g = torch.Generator().manual_seed(5)
+    codes = torch.randint(0, 128, (2, 22, 4), generator=g)
+    a = E.DecoderPlan(weights[0], 2, 22).run(codes=codes.cuda()).clone()
+    lat = O.pq_gather(codes, O.pq_codebooks(states[0])).transpose(1, 2).contiguous()
+    b = E.DecoderPlan(weights[0], 2, 22, from_latents=True).run(latents=lat.cuda())
+    assert torch.equal(a, b)
+
+
+def test_cfg3_logits_golden(gold, states, weights):
+    """BASELINE config 3 (reduced batch): one tokens_to_logits pass for given tokens and condition."""
+    from probtalk_b200 import engine as E
+    c = gold["cfg3"]
+    g = torch.Generator().manual_seed(c["seed"])
+    tokens = torch.randint(0, 129, (3, 22, 4), generator=g, dtype=torch.int32)
+    cond = torch.randn(3, 768, 22, generator=g)
+    plan = E.PredictorPlan(weights[1], weights[0], 3, 180)
+    plan.labels.copy_(c["label"].int())
+    # inject the condition directly (rows [B, T', 768]) and rebuild the memory K/V from it
+    plan.cond.valid().copy_(cond.transpose(1, 2))
+    for fn, args, _ in plan.plan_cond.steps[-2:]:
+        assert fn(*args, torch.cuda.current_stream().cuda_stream) == 0
+    plan.cur.copy_(tokens.view(3, -1))
+    plan.plan_iter.run()
+    logits = plan.logits.view(3, 22, 4, 128).cpu()
+    err = logits - c["logits"]
+    assert err.abs().max() < 0.12 and err.pow(2).mean().sqrt() < 0.02
+
+
+def test_context_encoder_vs_oracle(states, weights):
+    from probtalk_b200 import engine as E
+    B, T = 3, 180
+    aud, gt = S.synthetic_audio(B, T, 1003), S.synthetic_poses(B, T, 1004)
+    mask = torch.zeros(B, 1, T)
+    mask[:, :, 40:70] = 1
+    plan = E.PredictorPlan(weights[1], weights[0], B, T)
+    plan.aud.copy_(aud); plan.gt.copy_(gt); plan.mask.copy_(mask)
+    plan.run_condition()
+    _, cond_ref = O.predictor_condition(aud, gt, mask, states[1])
+    cond = plan.cond.valid().float().transpose(1, 2).cpu()
+    assert (cond - cond_ref).abs().max() < 0.2 and (cond - cond_ref).pow(2).mean().sqrt() < 0.02
+
+
+@pytest.mark.parametrize("step", [0, 2, 5, 7])
+def test_maskgit_step_vs_oracle(step):
+    """The sampler kernel against the oracle's restatement of sample_good's loop body, same injected noise."""
+    from probtalk_b200 import _lib, engine as E
+    B, N, T = 6, 88, 8
+    g = torch.Generator().manual_seed(40 + step)
+    logits = torch.randn(B, N, 128, generator=g) * 2
+    cur = torch.full((B, N), 128, dtype=torch.int32)
+    if step > 0:       # some tokens already decided
+        known = torch.rand(B, N, generator=g) < 0.1 * step
+        cur[known] = torch.randint(0, 128, (int(known.sum()),), generator=g, dtype=torch.int32)
+    u, gum = noise(T, B, N, 50 + step)
+    ref = O.maskgit_step(logits, cur, step, T, u[step], gum[step])
+    lg, cu, uu, gg = logits.cuda(), cur.cuda(), u[step].contiguous().cuda(), gum[step].contiguous().cuda()
+    out = torch.empty_like(cu)
+    E.check(_lib.lib().pt_maskgit_step(lg.data_ptr(), cu.data_ptr(), uu.data_ptr(), gg.data_ptr(), out.data_ptr(), B, N, 128,
+                                       128, E.maskgit_base_len(N, step, T), 4.5 * (1 - (step + 1) / T),
+                                       torch.cuda.current_stream().cuda_stream))
+    out = out.cpu()
+    assert int((out == 128).sum()) == int((ref == 128).sum())
+    # identical up to draws whose uniform lands within float rounding of a CDF boundary (none expected at this size)
+    assert int((out != ref).sum()) <= 1
+
+
+def test_cfg4_predictor_refiner_golden(gold, states, weights):
+    """BASELINE config 4 slice: predictor + refiner on one window with 30 known frames, sampler noise injected.
+    Hard sampling decisions amplify bf16 logit differences, so codes are compared statistically and poses are
+    compared for IDENTICAL codes (SURVEY.md 8c caveat 2)."""
+    from probtalk_b200 import engine as E
+    c = gold["cfg4"]
+    vq, pst, rst = states
+    B, T = c["B"], c["T"]
+    aud = S.synthetic_audio(1, T, c["aud_seed"]).repeat(B, 1, 1)
+    gt = S.synthetic_poses(B, T, c["gt_seed"])
+    mask = torch.zeros(B, 1, T)
+    mask[:, :, :30] = 1
+    u, gum = noise(8, B, 88, c["noise_seed"])
+    labels = torch.tensor([c["id"]] * B)
+    plan = E.PredictorPlan(weights[1], weights[0], B, T)
+    poses, codes = plan.run(aud.cuda(), gt.cuda(), mask.cuda(), labels.int().cuda(), noise=(u.cuda(), gum.cuda()))
+    poses, codes = poses.cpu(), codes.cpu()
+    assert codes.shape == (B, 22, 4) and int(codes.min()) >= 0 and int(codes.max()) < 128
+    agree = (codes.long() == c["codes"].long()).float().mean().item()
+    assert agree > 0.6, "free-running sampler diverged far more than bf16 logits explain (agreement %.2f)" % agree
+    # known frames are reproduced exactly: out = gt * mask * mask + pred * 0
+    assert torch.equal(poses[:, :, :30], gt[:, :, :30])
+    # identical codes -> tolerance-matched poses
+    tf = O.predictor_decode(codes.long(), gt * mask, mask, vq, T)
+    assert (poses - tf).abs().max() < 0.04
+    # the reference's codes through our decoder reproduce the reference's poses
+    plan.cur.copy_(c["codes"].int().view(B, -1))
+    ours_on_ref_codes = plan.run_decode().cpu()
+    assert (ours_on_ref_codes - c["poses"]).abs().max() < 0.04
+    assert per_joint_error(ours_on_ref_codes, c["poses"]) < 0.02
+    # refiner on the reference's predictor output vs the reference's refiner output
+    rp = E.RefinerPlan(weights[2], B, T, T)
+    out = rp.run(aud.cuda(), gt.cuda(), mask.cuda(), c["poses"].cuda(), labels.int().cuda()).cpu()
+    err = (out - c["refined"]).abs()
+    assert err.max() < 0.08 and err.mean() < 0.012
+    assert per_joint_error(out, c["refined"]) < 0.03
+    assert torch.equal(out[:, :, :30], gt[:, :, :30])
+
+
+def test_refiner_interpolates_shorter_prediction(states, weights):
+    """demo.py feeds 176-frame stage-1 output into 176-frame refiner windows; test_holisticbody feeds 180."""
+    from probtalk_b200 import engine as E
+    B, T, Tp = 2, 176, 144
+    aud, gt = S.synthetic_audio(B, T, 61), S.synthetic_poses(B, T, 62)
+    pred = S.synthetic_poses(B, Tp, 63)
+    mask = torch.zeros(B, 1, T)
+    mask[1, :, :30] = 1
+    labels = torch.tensor([0, 3])
+    out = E.RefinerPlan(weights[2], B, T, Tp).run(aud.cuda(), gt.cuda(), mask.cuda(), pred.cuda(), labels.int().cuda()).cpu()
+    ref = O.refiner_infer_on_batch(aud, gt, mask, labels, pred, states[2]["HFTransformer"])
+    assert (out - ref).abs().max() < 0.08
+
+
+def test_sampler_distribution_matches_oracle(states, weights):
+    """Distribution-level check of the free-running MaskGIT sampler: code histograms of the CUDA path and of the
+    oracle (independent noise) over 32 clips agree as well as two oracle runs agree with each other."""
+    from probtalk_b200 import engine as E
+    vq, pst, rst = states
+    B, T = 32, 180
+    aud, gt = S.synthetic_audio(B, T, 71), torch.zeros(B, 376, T)
+    mask = torch.zeros(B, 1, T)
+    labels = torch.arange(B) % 4
+    plan = E.PredictorPlan(weights[1], weights[0], B, T)
+    u, gum = noise(8, B, 88, 72)
+    _, codes_gpu = plan.run(aud.cuda(), gt.cuda(), mask.cuda(), labels.int().cuda(), noise=(u.cuda(), gum.cuda()))
+    codes_gpu = codes_gpu.cpu().long()
+    _, cond = O.predictor_condition(aud, gt, mask, pst)
+    dec = O._sub(pst["Predictor"], "decoder")
+    runs = []
+    for seed in (73, 74):
+        uu, gg = noise(8, B, 88, seed)
+        runs.append(O.sample_good(labels, cond, dec, 8, uu, gg).long())
+
+    def hist(cd):
+        return torch.stack([torch.bincount(cd[..., g].reshape(-1), minlength=128).float() for g in range(4)]) / cd[..., 0].numel()
+
+    tv_oracle = 0.5 * (hist(runs[0]) - hist(runs[1])).abs().sum(1).max().item()
+    tv_gpu = 0.5 * (hist(codes_gpu) - hist(runs[0])).abs().sum(1).max().item()
+    assert tv_gpu < 1.5 * tv_oracle + 0.05, (tv_gpu, tv_oracle)
+
+
+def test_wrapper_api_roundtrip(states):
+    """The reference-facing API: registry names, checkpoint dict layout, infer_on_batch chaining, VQ facade calls
+    made by scripts/demo.py:152-153."""
+    import types
+    import probtalk_b200.nets as nets
+    from bench import _config
+    vq, pst, rst = states
+    args = types.SimpleNamespace(gpu=0, infer=True)
+    model = nets.All_In_One_Model(None, None, ["s2g_body_predictor", "s2g_body_refiner"], [None, None], "cuda", args, _config())
+    pred, ref = model.body_model
+    pred.VQ.load_state_dict(vq)
+    pred.load_state_dict({"AudEnc": pst["AudEnc"], "Predictor": {"module." + k: v for k, v in pst["Predictor"].items()},
+                          "TextEnc": pst["TextEnc"], "generator_optim": None})
+    ref.load_state_dict(rst)
+    sd = pred.state_dict()
+    assert set(sd) == {"AudEnc", "Predictor", "TextEnc", "generator_optim"} and len(sd["Predictor"]) == 292
+    assert set(ref.state_dict()) == {"HFTransformer", "AudEnc", "generator_optim"}
+    B, T = 4, 180
+    aud1 = S.synthetic_audio(1, T, 81)
+    gt = S.synthetic_poses(1, T, 82).repeat(B, 1, 1)
+    mask = torch.zeros(B, 1, T)
+    out, seconds = model("infer_on_batch", aud=aud1.cuda(), text=aud1.cuda(), gt_poses=gt.cuda(), mask=mask.cuda(),
+                         id=torch.tensor([2]).cuda(), B=B)
+    assert out.shape == (B, 376, T) and seconds > 0 and bool(torch.isfinite(out).all())
+    poses, codes, _ = pred.infer_to_code(aud=aud1.cuda(), text=None, id=2, B=B, gt_poses=gt.cuda(), mask=mask.cuda())
+    assert codes.shape == (B, 22, 4)
+    lat = pred.VQ.vq_layer.quantize_all(codes).transpose(1, 2)            # demo.py:152
+    assert lat.shape == (B, 512, 22)
+    prelim = pred.VQ.decode(lat, None)                                    # demo.py:153
+    ref_dec = O.decoder_sc(O.pq_gather(codes.cpu().long(), O.pq_codebooks(vq)).transpose(1, 2).contiguous(), vq)
+    assert (prelim.cpu() - ref_dec).abs().max() < 0.04
+    # PQ-VAE wrapper (vq_teacher.infer_on_audio): encode -> quantise -> decode
+    vqt = nets.s2g_body_vqt(args, _config())
+    vqt.load_state_dict({"VQ": vq})
+    x = S.synthetic_poses(2, 300, 83)
+    rec, _ = vqt.infer_on_audio(gt_poses=x.cuda(), aud=None, text=None, id=None, B=1)
+    assert rec.shape == (2, 376, 296)
+    qo = vqt.VQ.vq_layer(torch.randn(2, 512, 9).cuda())
+    assert qo.quantized.shape == (2, 512, 9) and qo.loss.shape == (2, 9, 4)
