@@ -242,7 +242,7 @@ def run_ours(args):
                              "peak_source": pk["source"] + " bf16 sustained (kernel timed inside a long step)",
                              "launches_per_step": n_gemm, "gemm_ms_per_step": gemm_ms,
                              "kernel_share_of_step": kinds},
-                "whole_step_tflops": world * B * GFLOP_PER_CLIP / ms / 1e3 * 1e0,
+                "whole_step_tflops": world * B * GFLOP_PER_CLIP / ms,
                 "cpu_baseline": cpu, "e2e": e2e}
         print(json.dumps(line))
     if world > 1:

@@ -79,6 +79,7 @@ struct PqArgs {
   float* score_dump;            // [B*W, G, 128] or null (test hook)
   int* n_rescored;              // single counter or null (test hook)
   int rows_per_tile;
+  int rows_fast;                 // 1: channels-last rows, 16-byte aligned -> float4 row loader
 };
 
 template <bool kDump>
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   // ---- stage the query rows (row index math in 32 bits: tiles never span more than 2^31 rows)
   const int W = a.W;
   const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
-  if (a.zs_c == 1) {
+  if (a.rows_fast) {
     // channels-last rows: warp per row, float4 per lane; 16 rows in flight per warp
     constexpr int kPerWarp = kTileRows / (kThreads / 32);
     float4 xv[kPerWarp];
@@ -393,8 +394,6 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   if (B < 0 || W < 0) return pt::fail("pt_pq_search: negative shape");
   if ((long long)B * W == 0) return 0;
   if (!z || !codebooks || !idx_out) return pt::fail("pt_pq_search: null pointer");
-  if (zs_c == 1 && ((reinterpret_cast<uintptr_t>(z) & 15) || (zs_b & 3) || (zs_w & 3)))
-    return pt::fail("pt_pq_search: channels-last input must be 16-byte aligned with strides multiple of 4");
   if (reinterpret_cast<uintptr_t>(codebooks) & 15) return pt::fail("pt_pq_search: codebooks must be 16-byte aligned");
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -403,6 +402,7 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   a.z = z; a.zs_b = zs_b; a.zs_w = zs_w; a.zs_c = zs_c; a.B = B; a.W = W; a.G = G;
   a.codebooks = codebooks; a.idx_out = idx_out; a.gap_out = gap_out; a.score_dump = score_dump;
   a.n_rescored = n_rescored;
+  a.rows_fast = (zs_c == 1 && !(reinterpret_cast<uintptr_t>(z) & 15) && !(zs_b & 3) && !(zs_w & 3)) ? 1 : 0;
   const long long rows = (long long)B * W;
   a.rows_per_tile = choose_rows_per_tile(rows, G, sms);
   const size_t smem = sizeof(PqSmem) + 1024;
