@@ -94,7 +94,7 @@ int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);
  *   q   rows b*Nq + i, head h at columns [h*head_dim, (h+1)*head_dim), row stride q_stride elements
  *   k,v rows b*Nk + j, same column rule, strides k_stride / v_stride
  *   out rows b*Nq + i, row stride out_stride
- * head_dim must be 64, 1 <= Nk <= 192, Nq <= 1024. */
+ * head_dim must be 64, 1 <= Nk <= 1024 (K, V and Q of one (sample, head) must fit in shared memory), Nq <= 1024. */
 int pt_attention(const void* q, long long q_stride, const void* k, long long k_stride, const void* v,
                  long long v_stride, void* out, long long out_stride, int B, int heads, int head_dim, int Nq, int Nk,
                  float scale, void* stream);

@@ -4,7 +4,7 @@
 // (reference nets/inpainting/PTransformer.py:340 self-attention, :350 cross-attention): 8 heads x 64,
 // no masks, softmax over all keys.  Sequences on this path are tiny (88 tokens x 22 memory steps for the
 // predictor, 180 x 180 for the refiner), so one CTA owns one (sample, head): K, V and Q live in shared
-// memory, each warp owns 16-query blocks, scores stay in registers (whole-row softmax, no online rescale).
+// memory, each warp owns 16-query blocks and walks the keys in blocks of 64 with an online softmax.
 // Tensor-core work uses warp-level mma.sync m16n8k16 (bf16 in, fp32 accumulate): at <= 192 keys per head a
 // 128-row tcgen05 tile would be mostly padding; attention is < 10 % of the path's FLOPs.
 #include "pt_common.cuh"
@@ -37,11 +37,13 @@ struct AttnArgs {
   float scale_log2e;
 };
 
-// KT = number of 16-key steps kept in registers (keys padded to 16*KT)
-template <int KT>
-__global__ void __launch_bounds__(kWarps * 32) attention_kernel(AttnArgs a) {
+// Keys are processed in blocks of 64 with an online softmax (running max / sum, accumulator rescale), so the
+// register footprint is independent of the sequence length and several CTAs fit on an SM.
+constexpr int kKeyBlock = 64;
+
+__global__ void __launch_bounds__(kWarps * 32, 2) attention_kernel(AttnArgs a) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  constexpr int NKP = KT * 16;
+  const int NKP = ((a.Nk + kKeyBlock - 1) / kKeyBlock) * kKeyBlock;
   __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw);
   __nv_bfloat16* Vs = Ks + NKP * kRowPad;
   __nv_bfloat16* Qs = Vs + NKP * kRowPad;
@@ -73,7 +75,6 @@ __global__ void __launch_bounds__(kWarps * 32) attention_kernel(AttnArgs a) {
 
   const int g = lane >> 2, tig = lane & 3;
   for (int qb = warp; qb * 16 < a.Nq; qb += kWarps) {
-    // Q fragments for the 4 k-steps of the 64-wide head
     uint32_t qf[4][4];
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) {
@@ -83,58 +84,66 @@ __global__ void __launch_bounds__(kWarps * 32) attention_kernel(AttnArgs a) {
       qf[ks][2] = *reinterpret_cast<const uint32_t*>(q0 + 8);
       qf[ks][3] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kRowPad + 8);
     }
-    // S = Q K^T : 2*KT tiles of 8 keys
-    float sacc[2 * KT][4];
-#pragma unroll
-    for (int nt = 0; nt < 2 * KT; ++nt) {
-      sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
-#pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {
-        const __nv_bfloat16* kp = Ks + (nt * 8 + g) * kRowPad + ks * 16 + tig * 2;
-        mma_bf16(sacc[nt], qf[ks], *reinterpret_cast<const uint32_t*>(kp), *reinterpret_cast<const uint32_t*>(kp + 8));
-      }
-    }
-    // softmax over keys (rows g and g+8 of the block; a row is spread over the 4 lanes of a quad)
-    float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-    for (int nt = 0; nt < 2 * KT; ++nt) {
-      const int key = nt * 8 + tig * 2;
-      if (key >= a.Nk) { sacc[nt][0] = -INFINITY; sacc[nt][2] = -INFINITY; }
-      if (key + 1 >= a.Nk) { sacc[nt][1] = -INFINITY; sacc[nt][3] = -INFINITY; }
-      mx0 = fmaxf(mx0, fmaxf(sacc[nt][0], sacc[nt][1]));
-      mx1 = fmaxf(mx1, fmaxf(sacc[nt][2], sacc[nt][3]));
-    }
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    float sum0 = 0.f, sum1 = 0.f;
-    uint32_t pf[2 * KT][2];
-#pragma unroll
-    for (int nt = 0; nt < 2 * KT; ++nt) {
-      const float p0 = exp2f((sacc[nt][0] - mx0) * a.scale_log2e), p1 = exp2f((sacc[nt][1] - mx0) * a.scale_log2e);
-      const float p2 = exp2f((sacc[nt][2] - mx1) * a.scale_log2e), p3 = exp2f((sacc[nt][3] - mx1) * a.scale_log2e);
-      sum0 += p0 + p1; sum1 += p2 + p3;
-      pf[nt][0] = pt::pack_bf16x2(p0, p1);
-      pf[nt][1] = pt::pack_bf16x2(p2, p3);
-    }
-    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
-    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
-    // O = P V
+    float mx0 = -INFINITY, mx1 = -INFINITY, sum0 = 0.f, sum1 = 0.f;
     float oacc[8][4];
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) oacc[nt][0] = oacc[nt][1] = oacc[nt][2] = oacc[nt][3] = 0.f;
+
+    for (int kb = 0; kb < NKP; kb += kKeyBlock) {
+      // S = Q K^T for 64 keys: 8 tiles of 8 keys
+      float sacc[8][4];
 #pragma unroll
-    for (int kt = 0; kt < KT; ++kt) {
-      const uint32_t af[4] = {pf[2 * kt][0], pf[2 * kt][1], pf[2 * kt + 1][0], pf[2 * kt + 1][1]};
+      for (int nt = 0; nt < 8; ++nt) {
+        sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
 #pragma unroll
-      for (int np = 0; np < 4; ++np) {       // pairs of 8-wide dim tiles
-        uint32_t bf[4];
-        // lanes 0-7: keys kt*16+0..7 @ dim np*16 ; 8-15: keys +8 ; 16-23: keys 0..7 @ dim np*16+8 ; 24-31: keys +8
-        const __nv_bfloat16* vp = Vs + (kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * kRowPad + np * 16 + (lane >> 4) * 8;
-        ldmatrix_x4_trans(bf, vp);
-        mma_bf16(oacc[2 * np], af, bf[0], bf[1]);
-        mma_bf16(oacc[2 * np + 1], af, bf[2], bf[3]);
+        for (int ks = 0; ks < 4; ++ks) {
+          const __nv_bfloat16* kp = Ks + (kb + nt * 8 + g) * kRowPad + ks * 16 + tig * 2;
+          mma_bf16(sacc[nt], qf[ks], *reinterpret_cast<const uint32_t*>(kp), *reinterpret_cast<const uint32_t*>(kp + 8));
+        }
+      }
+      float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int key = kb + nt * 8 + tig * 2;
+        if (key >= a.Nk) { sacc[nt][0] = -INFINITY; sacc[nt][2] = -INFINITY; }
+        if (key + 1 >= a.Nk) { sacc[nt][1] = -INFINITY; sacc[nt][3] = -INFINITY; }
+        bm0 = fmaxf(bm0, fmaxf(sacc[nt][0], sacc[nt][1]));
+        bm1 = fmaxf(bm1, fmaxf(sacc[nt][2], sacc[nt][3]));
+      }
+      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1)); bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1)); bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+      const float nm0 = fmaxf(mx0, bm0), nm1 = fmaxf(mx1, bm1);       // finite: the first block always has a valid key
+      const float sc0 = exp2f((mx0 - nm0) * a.scale_log2e), sc1 = exp2f((mx1 - nm1) * a.scale_log2e);
+      mx0 = nm0; mx1 = nm1;
+      sum0 *= sc0; sum1 *= sc1;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) { oacc[nt][0] *= sc0; oacc[nt][1] *= sc0; oacc[nt][2] *= sc1; oacc[nt][3] *= sc1; }
+      uint32_t pf[8][2];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const float p0 = exp2f((sacc[nt][0] - mx0) * a.scale_log2e), p1 = exp2f((sacc[nt][1] - mx0) * a.scale_log2e);
+        const float p2 = exp2f((sacc[nt][2] - mx1) * a.scale_log2e), p3 = exp2f((sacc[nt][3] - mx1) * a.scale_log2e);
+        sum0 += p0 + p1; sum1 += p2 + p3;
+        pf[nt][0] = pt::pack_bf16x2(p0, p1);
+        pf[nt][1] = pt::pack_bf16x2(p2, p3);
+      }
+      // O += P V for this key block
+#pragma unroll
+      for (int kt = 0; kt < 4; ++kt) {
+        const uint32_t af[4] = {pf[2 * kt][0], pf[2 * kt][1], pf[2 * kt + 1][0], pf[2 * kt + 1][1]};
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+          uint32_t bf[4];
+          // lanes 0-7: keys +0..7 @ dim np*16 ; 8-15: keys +8..15 ; 16-23: keys +0..7 @ dim np*16+8 ; 24-31: keys +8..15
+          const __nv_bfloat16* vp = Vs + (kb + kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * kRowPad + np * 16 + (lane >> 4) * 8;
+          ldmatrix_x4_trans(bf, vp);
+          mma_bf16(oacc[2 * np], af, bf[0], bf[1]);
+          mma_bf16(oacc[2 * np + 1], af, bf[2], bf[3]);
+        }
       }
     }
+    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
     const float inv0 = 1.f / sum0, inv1 = 1.f / sum1;
     const int r0 = qb * 16 + g, r1 = r0 + 8;
     __nv_bfloat16* o0 = a.out + ((size_t)b * a.Nq + r0) * a.out_stride + h * kHeadDim + tig * 2;
@@ -147,16 +156,16 @@ __global__ void __launch_bounds__(kWarps * 32) attention_kernel(AttnArgs a) {
   }
 }
 
-template <int KT>
 int launch_attn(const AttnArgs& a, int B, cudaStream_t st) {
   const int NQP = (a.Nq + 15) & ~15;
-  const size_t smem = (size_t)(2 * KT * 16 + NQP) * kRowPad * sizeof(__nv_bfloat16);
+  const int NKP = ((a.Nk + kKeyBlock - 1) / kKeyBlock) * kKeyBlock;
+  const size_t smem = (size_t)(2 * NKP + NQP) * kRowPad * sizeof(__nv_bfloat16);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    PT_CUDA(cudaFuncSetAttribute(attention_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PT_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  attention_kernel<KT><<<B * a.heads, kWarps * 32, smem, st>>>(a);
+  attention_kernel<<<B * a.heads, kWarps * 32, smem, st>>>(a);
   PT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -169,7 +178,7 @@ extern "C" int pt_attention(const void* q, long long q_stride, const void* k, lo
   if (B <= 0 || Nq <= 0) return 0;
   if (!q || !k || !v || !out) return pt::fail("pt_attention: null pointer");
   if (head_dim != kHeadDim) return pt::fail("pt_attention: only head_dim 64 is built (got %d)", head_dim);
-  if (Nk <= 0 || Nk > 192) return pt::fail("pt_attention: 1..192 keys per head supported (got %d)", Nk);
+  if (Nk <= 0 || Nk > 1024) return pt::fail("pt_attention: 1..1024 keys per head supported (got %d)", Nk);
   if (Nq > 1024) return pt::fail("pt_attention: at most 1024 queries per sample (got %d)", Nq);
   if ((q_stride | k_stride | v_stride) & 7) return pt::fail("pt_attention: row strides must be multiples of 8 elements");
   if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15)
@@ -182,7 +191,5 @@ extern "C" int pt_attention(const void* q, long long q_stride, const void* k, lo
   a.heads = heads; a.Nq = Nq; a.Nk = Nk;
   a.scale_log2e = scale * 1.4426950408889634f;
   cudaStream_t st = (cudaStream_t)stream;
-  if (Nk <= 32) return launch_attn<2>(a, B, st);
-  if (Nk <= 96) return launch_attn<6>(a, B, st);
-  return launch_attn<12>(a, B, st);
+  return launch_attn(a, B, st);
 }

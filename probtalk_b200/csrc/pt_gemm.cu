@@ -36,7 +36,8 @@ struct Cfg {
   static constexpr uint32_t kBBytes = BN * BK * 2;          // 16 / 32 KB
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;             // double-buffered accumulator
-  static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256;
+  static constexpr size_t kEpiBytes = 4 * (32 * 33 * 4 + 64 * 8);   // per-warp transpose tile + row offset table
+  static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256 + kEpiBytes;
 };
 
 struct GemmKernelArgs {
@@ -77,6 +78,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   uint64_t* tmem_full = bars + 2 * C::kStages;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  long long* rowoff_base = reinterpret_cast<long long*>(smem + (size_t)C::kStages * C::kStageBytes + 256);
+  float* stage_base = reinterpret_cast<float*>(rowoff_base + 4 * 64);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tiles_total = p.m_tiles * p.N_tiles;
@@ -145,8 +148,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
   } else if (warp >= kEpiWarp0) {
     // ------------------------------------------------------------ epilogue
+    // TMEM hands every thread one output ROW (32 consecutive columns per tcgen05.ld).  Row-major global accesses
+    // in that layout touch 32 different cache lines per instruction, so each 32x32 chunk is transposed through a
+    // per-warp padded smem tile: afterwards a lane owns a COLUMN, one bias value lives in a register, and
+    // residual loads / output stores are fully coalesced row segments.
     const int q = warp & 3;                              // TMEM lane quadrant this warp may touch
+    float* stage = stage_base + q * (32 * 33);
+    long long* row_out = rowoff_base + q * 64;           // [32] output row offsets (or -1), [32] residual offsets
+    long long* row_res = row_out + 32;
     int acc = 0; uint32_t acc_phase = 0;
+    const bool row_major = (p.ocs == 1);
     for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
       const int m0 = (tile / p.N_tiles) * BM, n0 = (tile % p.N_tiles) * BN;
       const int m = m0 + q * 32 + lane;
@@ -154,83 +165,100 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const bool row_ok = (m < p.M) && (t < p.t_valid);
       const long long obase = (long long)b * p.oss + (long long)t * p.ors;
       const long long rbase = (long long)b * p.rss + (long long)t * p.rrs;
+      __syncwarp();
+      row_out[lane] = row_ok ? obase : -1;
+      row_res[lane] = rbase;
+      __syncwarp();
       pt::mbar_wait(&tmem_full[acc], acc_phase);
       pt::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int n = n0 + c0;
+        if (n >= p.n_valid) break;                       // warp-uniform
         uint32_t v[32];
         pt::tmem_ld32(t_row + c0, v);
         pt::tmem_ld_wait();
-        const int n = n0 + c0;
-        if (row_ok && n < p.n_valid) {
-          float f[32];
+        if (!row_major) {
+          // channel-major output (final projections): lanes = consecutive rows -> already coalesced per column
+          if (row_ok) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.bias) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + n + i);
-          }
-          if (p.residual) {
-            if (p.res_f32) {
-              const float4* r = reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + rbase + n);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                float4 x = __ldg(r + i);
-                f[4 * i] += x.x; f[4 * i + 1] += x.y; f[4 * i + 2] += x.z; f[4 * i + 3] += x.w;
-              }
-            } else {
-              const uint4* r = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rbase + n);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                uint4 x = __ldg(r + i);
-                const uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[j]);
-                  f[8 * i + 2 * j] += __bfloat162float(h.x);
-                  f[8 * i + 2 * j + 1] += __bfloat162float(h.y);
-                }
+            for (int i = 0; i < 32; ++i) {
+              if (n + i < p.n_valid) {
+                float f = __uint_as_float(v[i]) + (p.bias ? __ldg(p.bias + n + i) : 0.f);
+                f = apply_act(f, p.act, p.slope);
+                const long long off = obase + (long long)(n + i) * p.ocs;
+                if (p.out_f32) static_cast<float*>(p.out)[off] = f;
+                else static_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(f);
               }
             }
           }
-          if (p.act == PT_ACT_GATE) {
-            // interleaved columns (a0,b0,a1,b1,...) -> tanh(a) * sigmoid(b), 16 outputs at column n/2
-            float gt[16];
+          continue;
+        }
+        __syncwarp();
 #pragma unroll
-            for (int i = 0; i < 16; ++i) gt[i] = tanhf(f[2 * i]) * (1.f / (1.f + __expf(-f[2 * i + 1])));
-            __nv_bfloat16* o = static_cast<__nv_bfloat16*>(p.out) + obase + (n >> 1);
-            uint4 w0 = make_uint4(pt::pack_bf16x2(gt[0], gt[1]), pt::pack_bf16x2(gt[2], gt[3]),
-                                  pt::pack_bf16x2(gt[4], gt[5]), pt::pack_bf16x2(gt[6], gt[7]));
-            uint4 w1 = make_uint4(pt::pack_bf16x2(gt[8], gt[9]), pt::pack_bf16x2(gt[10], gt[11]),
-                                  pt::pack_bf16x2(gt[12], gt[13]), pt::pack_bf16x2(gt[14], gt[15]));
-            reinterpret_cast<uint4*>(o)[0] = w0;
-            reinterpret_cast<uint4*>(o)[1] = w1;
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = apply_act(f[i], p.act, p.slope);
-            if (p.ocs == 1 && n + 32 <= p.n_valid) {
-              if (p.out_f32) {
-                float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + obase + n);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) o[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
-              } else {
-                uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + obase + n);
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                  o[i] = make_uint4(pt::pack_bf16x2(f[8 * i], f[8 * i + 1]), pt::pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
-                                    pt::pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pt::pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+        for (int i = 0; i < 32; ++i) stage[lane * 33 + i] = __uint_as_float(v[i]);
+        __syncwarp();
+        if (p.act == PT_ACT_GATE) {
+          // interleaved columns (a0,b0,a1,b1,...): even lanes tanh(a), odd lanes sigmoid(b), product on even lanes
+          const float bv = p.bias ? __ldg(p.bias + n + lane) : 0.f;
+          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(p.out) + ((n + lane) >> 1);
+#pragma unroll 4
+          for (int rr = 0; rr < 32; ++rr) {
+            const float x = stage[rr * 33 + lane] + bv;
+            const float f = (lane & 1) ? 1.f / (1.f + __expf(-x)) : tanhf(x);
+            const float pr = f * __shfl_xor_sync(0xffffffffu, f, 1);
+            const float pr2 = __shfl_down_sync(0xffffffffu, pr, 2);
+            const long long ro = row_out[rr];
+            if (ro >= 0 && (lane & 3) == 0) *reinterpret_cast<uint32_t*>(o + ro) = pt::pack_bf16x2(pr, pr2);
+          }
+        } else if (p.out_f32) {
+          // one lane per column, one row per iteration: 128 B stores
+          const int col = n + lane;
+          const bool col_ok = col < p.n_valid;
+          const float bv = (p.bias && col_ok) ? __ldg(p.bias + col) : 0.f;
+          float* o = static_cast<float*>(p.out) + col;
+#pragma unroll 8
+          for (int rr = 0; rr < 32; ++rr) {
+            const long long ro = row_out[rr];
+            float x = stage[rr * 33 + lane] + bv;
+            if (ro >= 0 && col_ok) {
+              if (p.residual) {
+                x += p.res_f32 ? __ldg(static_cast<const float*>(p.residual) + row_res[rr] + col)
+                               : __bfloat162float(static_cast<const __nv_bfloat16*>(p.residual)[row_res[rr] + col]);
               }
-            } else {
-              // strided / ragged columns: lanes hold consecutive rows, so a channel-first output is coalesced
-#pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                if (n + i < p.n_valid) {
-                  const long long off = obase + (long long)(n + i) * p.ocs;
-                  if (p.out_f32) static_cast<float*>(p.out)[off] = f[i];
-                  else static_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(f[i]);
+              o[ro] = apply_act(x, p.act, p.slope);
+            }
+          }
+        } else {
+          // bf16 output: half a warp per row, two columns per lane: 64 B stores, two rows per iteration
+          const int hl = lane & 15, hr = lane >> 4;
+          const int col = n + 2 * hl;
+          const bool c0_ok = col < p.n_valid, c1_ok = col + 1 < p.n_valid;
+          const float b0 = (p.bias && c0_ok) ? __ldg(p.bias + col) : 0.f;
+          const float b1 = (p.bias && c1_ok) ? __ldg(p.bias + col + 1) : 0.f;
+          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(p.out) + col;
+#pragma unroll 4
+          for (int r2 = 0; r2 < 32; r2 += 2) {
+            const int rr = r2 + hr;
+            const long long ro = row_out[rr];
+            float x0 = stage[rr * 33 + 2 * hl] + b0, x1 = stage[rr * 33 + 2 * hl + 1] + b1;
+            if (ro >= 0 && c0_ok) {
+              if (p.residual) {
+                if (p.res_f32) {
+                  const float* r = static_cast<const float*>(p.residual) + row_res[rr] + col;
+                  x0 += __ldg(r);
+                  if (c1_ok) x1 += __ldg(r + 1);
+                } else {
+                  const __nv_bfloat16* r = static_cast<const __nv_bfloat16*>(p.residual) + row_res[rr] + col;
+                  x0 += __bfloat162float(r[0]);
+                  if (c1_ok) x1 += __bfloat162float(r[1]);
                 }
               }
+              x0 = apply_act(x0, p.act, p.slope);
+              x1 = apply_act(x1, p.act, p.slope);
+              if (c1_ok) *reinterpret_cast<uint32_t*>(o + ro) = pt::pack_bf16x2(x0, x1);
+              else o[ro] = __float2bfloat16_rn(x0);
             }
           }
         }

@@ -1,0 +1,183 @@
+"""Unit parity of the individual CUDA entry points (through the C ABI) against plain PyTorch fp32 on the same
+(bf16-rounded) inputs.  These are floating-point kernels, so the checker is a torch fp32 reference; tolerances are
+those of bf16 outputs (rel 2^-8) or fp32 accumulation-order noise."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1000, 256, 512), (333, 384, 1024), (4100, 1536, 512), (50, 2048, 512)])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_gemm_plain(M, N, K, out_dtype):
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=out_dtype)
+    ops.gemm(a, w, out, M=M, C_=K, bias=bias, ors=N)
+    ref = a.float() @ w.float().t() + bias
+    tol = 1e-4 if out_dtype == torch.float32 else 0.03
+    assert (out.float() - ref).abs().max() < tol
+
+
+def test_gemm_ragged_n_residual_and_acts():
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(3)
+    M, K, N, Npad = 777, 256, 376, 384
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = torch.zeros(Npad, K, device="cuda")
+    w[:N] = torch.randn(N, K, device="cuda", generator=g) / K ** 0.5
+    w = w.bfloat16()
+    bias = torch.zeros(Npad, device="cuda")
+    bias[:N] = torch.randn(N, device="cuda", generator=g)
+    ref = a.float() @ w[:N].float().t() + bias[:N]
+    for res_dtype in (None, torch.float32, torch.bfloat16):
+        for out_dtype in (torch.float32, torch.bfloat16):
+            for act, fn in ((ops.ACT_NONE, lambda x: x), (ops.ACT_RELU, torch.relu), (ops.ACT_LEAKY, lambda x: F.leaky_relu(x, 0.2))):
+                res = None if res_dtype is None else torch.randn(M, N, device="cuda", generator=g).to(res_dtype)
+                out = torch.full((M, N), 7.0, device="cuda", dtype=out_dtype)
+                ops.gemm(a, w, out, M=M, C_=K, bias=bias, n_valid=N, ors=N, residual=res, rrs=N, act=act)
+                r = fn(ref + (0 if res is None else res.float()))
+                tol = 2e-4 if out_dtype == torch.float32 else 0.04
+                assert (out.float() - r).abs().max() < tol, (res_dtype, out_dtype, act)
+
+
+def test_gemm_conv_taps_strides_and_transposed():
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(2)
+    B, T, Cin, Cout, H = 5, 45, 128, 256, 1
+    x = torch.randn(B, Cin, T, device="cuda", generator=g)
+    Tp = T + 2 * H + ((T + 2 * H) % 2)
+    xb = torch.zeros(B, Tp, Cin, device="cuda", dtype=torch.bfloat16)
+    xb[:, H:H + T] = x.transpose(1, 2).bfloat16()
+    xr = xb[:, H:H + T].float().transpose(1, 2)
+    bias = torch.randn(Cout, device="cuda", generator=g)
+    # k3 s1 p1
+    w3 = (torch.randn(Cout, Cin, 3, device="cuda", generator=g) / (3 * Cin) ** 0.5).bfloat16()
+    out = torch.zeros(B, Tp, Cout, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(xb.view(-1), w3.permute(0, 2, 1).reshape(Cout, -1).contiguous(), out.view(-1), M=B * Tp, C_=Cin, taps=3,
+             base_row=H - 1, rows_per_sample=Tp, t_valid=T, oss=Tp * Cout, ors=Cout, out_offset=H * Cout, bias=bias,
+             act=ops.ACT_LEAKY)
+    ref = F.leaky_relu(F.conv1d(xr, w3.float(), bias, padding=1), 0.2)
+    assert (out[:, H:H + T].float().transpose(1, 2) - ref).abs().max() < 0.04
+    assert float(out[:, :H].abs().max()) == 0 and float(out[:, H + T:].abs().max()) == 0        # halo rows untouched
+    # k4 s2 p1
+    w4 = (torch.randn(Cout, Cin, 4, device="cuda", generator=g) / (4 * Cin) ** 0.5).bfloat16()
+    To = (T - 2) // 2 + 1
+    out2 = torch.zeros(B, To + 2, Cout, device="cuda")
+    ops.gemm(xb.view(-1), w4.permute(0, 2, 1).reshape(Cout, -1).contiguous(), out2.view(-1), M=B * (Tp // 2), C_=Cin,
+             taps=4, s=2, base_row=0, rows_per_sample=Tp // 2, t_valid=To, oss=(To + 2) * Cout, ors=Cout, out_offset=Cout,
+             bias=bias)
+    ref2 = F.conv1d(xr, w4.float(), bias, stride=2, padding=1)
+    assert (out2[:, 1:1 + To].transpose(1, 2) - ref2).abs().max() < 2e-4
+    # transposed k4 s2 p1, channel-first fp32 output
+    wt = (torch.randn(Cin, Cout, 4, device="cuda", generator=g) / (2 * Cin) ** 0.5).bfloat16()
+    outT = torch.zeros(B, Cout, 2 * T, device="cuda")
+    for ph, taps in enumerate(((3, 1), (2, 0))):
+        wk = torch.cat([wt[:, :, taps[0]].t(), wt[:, :, taps[1]].t()], dim=1).contiguous()
+        ops.gemm(xb.view(-1), wk, outT.view(-1), M=B * Tp, C_=Cin, taps=2, base_row=H - 1 + ph, rows_per_sample=Tp,
+                 t_valid=T, oss=Cout * 2 * T, ors=2, ocs=2 * T, out_offset=ph, bias=bias)
+    refT = F.conv_transpose1d(xr, wt.float(), bias, stride=2, padding=1)
+    assert (outT - refT).abs().max() < 2e-4
+
+
+def test_gemm_gated_epilogue():
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(4)
+    M, Cc = 700, 256
+    a = torch.randn(M, Cc, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(2 * Cc, Cc, device="cuda", generator=g) / Cc ** 0.5).bfloat16()
+    b2 = torch.randn(2 * Cc, device="cuda", generator=g)
+    wi = torch.stack([w[:Cc], w[Cc:]], dim=1).reshape(2 * Cc, Cc).contiguous()
+    bi = torch.stack([b2[:Cc], b2[Cc:]], dim=1).reshape(-1).contiguous()
+    out = torch.zeros(M, Cc, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a, wi, out, M=M, C_=Cc, bias=bi, act=ops.ACT_GATE, ors=Cc)
+    h = a.float() @ w.float().t() + b2
+    ref = torch.tanh(h[:, :Cc]) * torch.sigmoid(h[:, Cc:])
+    assert (out.float() - ref).abs().max() < 0.01
+
+
+@pytest.mark.parametrize("Nq,Nk", [(88, 88), (88, 22), (180, 180), (5, 3), (17, 65), (48, 48), (200, 300)])
+def test_attention(Nq, Nk):
+    from probtalk_b200 import _lib
+    B, Hh, D = 3, 8, 64
+    g = torch.Generator(device="cuda").manual_seed(Nq * 7 + Nk)
+    q = torch.randn(B * Nq, Hh * D, device="cuda", generator=g).bfloat16()
+    kv = torch.randn(B * Nk, 2 * Hh * D, device="cuda", generator=g).bfloat16()
+    out = torch.zeros(B * Nq, Hh * D, device="cuda", dtype=torch.bfloat16)
+    rc = _lib.lib().pt_attention(q.data_ptr(), Hh * D, kv.data_ptr(), 2 * Hh * D, kv.data_ptr() + 2 * Hh * D, 2 * Hh * D,
+                                 out.data_ptr(), Hh * D, B, Hh, D, Nq, Nk, 1.0 / math.sqrt(D), _st())
+    _lib.check(rc)
+    qf = q.float().view(B, Nq, Hh, D).transpose(1, 2)
+    kf = kv[:, :Hh * D].float().view(B, Nk, Hh, D).transpose(1, 2)
+    vf = kv[:, Hh * D:].float().view(B, Nk, Hh, D).transpose(1, 2)
+    ref = torch.softmax(qf @ kf.transpose(-1, -2) / math.sqrt(D), -1) @ vf
+    ref = ref.transpose(1, 2).reshape(B * Nq, Hh * D)
+    assert (out.float() - ref).abs().max() < 0.03
+
+
+def test_layernorm_kernels_and_embed():
+    from probtalk_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator(device="cuda").manual_seed(9)
+    M, N = 1000, 88
+    x = torch.randn(M, 512, device="cuda", generator=g) * 3 + 1
+    gamma, beta = torch.rand(512, device="cuda", generator=g) + 0.5, torch.randn(512, device="cuda", generator=g)
+    o32, o16 = torch.zeros(M, 512, device="cuda"), torch.zeros(M, 512, device="cuda", dtype=torch.bfloat16)
+    _lib.check(L.pt_layernorm512(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), o32.data_ptr(), o16.data_ptr(), M, _st()))
+    ref = F.layer_norm(x, (512,), gamma, beta, 1e-5)
+    assert (o32 - ref).abs().max() < 2e-5 and (o16.float() - ref).abs().max() < 0.05
+    # style modulation: labels per sample of 8 rows, 4 classes
+    mod = torch.randn(4, 1024, device="cuda", generator=g) * 0.5
+    labels = (torch.arange(M // 8, device="cuda") % 4).int()
+    xb = x.bfloat16()
+    out = torch.zeros(M, 512, device="cuda", dtype=torch.bfloat16)
+    _lib.check(L.pt_ln_mod_silu512(xb.data_ptr(), 0, gamma.data_ptr(), beta.data_ptr(), mod.data_ptr(), labels.data_ptr(), 8,
+                                   out.data_ptr(), M, _st()))
+    m = mod[labels.long()].repeat_interleave(8, 0)
+    y = F.layer_norm(xb.float(), (512,), gamma, beta, 1e-5) * (1 + m[:, :512]) + m[:, 512:]
+    assert (out.float() - F.silu(y)).abs().max() < 0.06
+    # embedding + fp64 positional table, rounded like (x + pe).to(float32)
+    emb = torch.randn(129, 512, device="cuda", generator=g)
+    pe = torch.randn(N, 512, device="cuda", generator=g, dtype=torch.float64)
+    tok = torch.randint(0, 129, (M // N * N,), device="cuda", generator=g, dtype=torch.int32)
+    e32 = torch.zeros(tok.numel(), 512, device="cuda")
+    bad = torch.zeros(1, device="cuda", dtype=torch.int32)
+    _lib.check(L.pt_embed_tokens512(tok.data_ptr(), emb.data_ptr(), 129, pe.data_ptr(), N, e32.data_ptr(), None, tok.numel(),
+                                    bad.data_ptr(), _st()))
+    ref = (emb[tok.long()].double() + pe.repeat(tok.numel() // N, 1)).float()
+    assert torch.equal(e32, ref) and int(bad) == 0
+
+
+def test_pack_and_blend_match_torch():
+    from probtalk_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator(device="cuda").manual_seed(10)
+    B, Cc, T, Tpred = 3, 376, 180, 176
+    src = torch.randn(B, Cc, T, device="cuda", generator=g)
+    pred = torch.randn(B, Cc, Tpred, device="cuda", generator=g)
+    mask = (torch.rand(B, 1, T, device="cuda", generator=g) < 0.3).float()
+    H, Cp = 1, 384
+    Tp = T + 2
+    dst = torch.zeros(B, Tp, Cp, device="cuda", dtype=torch.bfloat16)
+    _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), Tpred, dst.data_ptr(), B, Cc, T, Tp, H, Cp, 0, 2, _st()))
+    interp = F.interpolate(pred, size=T, mode="linear")
+    ref = src * mask + interp * (1 - mask)
+    got = dst[:, H:H + T, :Cc].float().transpose(1, 2)
+    assert (got - ref.bfloat16().float()).abs().max() < 0.02
+    assert float(dst[:, :, Cc:].abs().max()) == 0 and float(dst[:, 0].abs().max()) == 0
+    _lib.check(L.pt_pack_mask(mask.data_ptr(), dst.data_ptr(), B, T, Tp, H, Cp, Cc, 1, _st()))
+    oh = F.one_hot(mask.long(), 2).squeeze(1).float()
+    assert torch.equal(dst[:, H:H + T, Cc:Cc + 2].float(), oh)
+    out = torch.zeros(B, Cc, T, device="cuda")
+    _lib.check(L.pt_interp_blend(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), Tpred, out.data_ptr(), B, Cc, T, 2, _st()))
+    assert (out - (src * mask * mask + interp * (1 - mask))).abs().max() < 1e-5
