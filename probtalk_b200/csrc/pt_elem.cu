@@ -132,7 +132,8 @@ __device__ __forceinline__ void ln_stats(const float (&v)[16], float& mean, floa
 }
 
 // nn.LayerNorm (norm1/2/3 of DeepSupervisionLayer, PTransformer.py:329-331): fp32 in -> fp32 and/or bf16 out
-__global__ void ln_kernel(const float* __restrict__ in, const float* __restrict__ gamma, const float* __restrict__ beta,
+template <typename InT>
+__global__ void ln_kernel(const InT* __restrict__ in, const float* __restrict__ gamma, const float* __restrict__ beta,
                           float* __restrict__ out32, __nv_bfloat16* __restrict__ out16, int M) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -316,11 +317,14 @@ extern "C" int pt_interp_blend(const float* known, const float* mask, const floa
   return 0;
 }
 
-extern "C" int pt_layernorm512(const float* in, const float* gamma, const float* beta, float* out_f32, void* out_bf16,
-                               int M, void* stream) {
+extern "C" int pt_layernorm512(const void* in, int in_f32, const float* gamma, const float* beta, float* out_f32,
+                               void* out_bf16, int M, void* stream) {
   if (M <= 0) return 0;
   if (!in || !gamma || !beta || (!out_f32 && !out_bf16)) return pt::fail("pt_layernorm512: null pointer");
-  ln_kernel<<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>(in, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
+  if (in_f32)
+    ln_kernel<float><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const float*)in, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
+  else
+    ln_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
   PT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -11,11 +11,11 @@
 //  nets/inpainting/PTransformer.py:284-372).  A is bf16 [rows, C] row-major (K-major), W is bf16 [N, taps*C]
 // K-major; accumulation is fp32 in TMEM.
 //
-// Warp roles (256 threads, 1 CTA / SM, persistent over 128 x BN output tiles):
+// Warp roles (384 threads, 1 CTA / SM, persistent over 128 x BN output tiles):
 //   warp 0  TMA producer: per K-step one 128x64 A box + one BNx64 W box (SWIZZLE_128B) into a smem ring
 //   warp 1  MMA issuer  : one thread, 4 x tcgen05.mma (K=16 each) per K-step, tcgen05.commit frees the slot
 //   warp 2  TMEM allocator (2 accumulator stages x BN columns)
-//   warps 4-7 epilogue  : tcgen05.ld (lane = output row), bias / residual / activation, direct global stores
+//   warps 4-11 epilogue : tcgen05.ld (lane = output row), bias / residual / activation, smem-staged 64-byte row stores
 // so the epilogue of tile i overlaps the main loop of tile i+1.
 #include <cuda.h>
 #include "pt_common.cuh"
@@ -26,8 +26,10 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
-constexpr int kThreads = 256;
 constexpr int kEpiWarp0 = 4;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = (kEpiWarp0 + kEpiWarps) * 32;   // 384
+constexpr int kTilePitch = 80;                          // 64 B payload + 16 B pad: conflict-free 16-byte accesses
 
 template <int BN>
 struct Cfg {
@@ -36,8 +38,7 @@ struct Cfg {
   static constexpr uint32_t kBBytes = BN * BK * 2;          // 16 / 32 KB
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;             // double-buffered accumulator
-  static constexpr size_t kEpiBytes = 4 * (32 * 33 * 4 + 64 * 8);   // per-warp transpose tile + row offset table
-  static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256 + kEpiBytes;
+  static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256;   // + 24 KB static (epilogue staging)
 };
 
 struct GemmKernelArgs {
@@ -78,8 +79,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   uint64_t* tmem_full = bars + 2 * C::kStages;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  long long* rowoff_base = reinterpret_cast<long long*>(smem + (size_t)C::kStages * C::kStageBytes + 256);
-  float* stage_base = reinterpret_cast<float*>(rowoff_base + 4 * 64);
+  // epilogue staging lives in STATIC shared memory so the compiler emits LDS/STS (pointers carved from the
+  // dynamic buffer lose their address space and become slow generic loads)
+  __shared__ __align__(16) uint8_t tile_s[kEpiWarps][32 * kTilePitch];
+  __shared__ long long rowoff_s[kEpiWarps][64];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tiles_total = p.m_tiles * p.N_tiles;
@@ -90,7 +93,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], kEpiWarps); }
     pt::fence_mbar_init();
   }
   if (warp == 2) {
@@ -147,119 +150,167 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       }
     }
   } else if (warp >= kEpiWarp0) {
-    // ------------------------------------------------------------ epilogue
-    // TMEM hands every thread one output ROW (32 consecutive columns per tcgen05.ld).  Row-major global accesses
-    // in that layout touch 32 different cache lines per instruction, so each 32x32 chunk is transposed through a
-    // per-warp padded smem tile: afterwards a lane owns a COLUMN, one bias value lives in a register, and
-    // residual loads / output stores are fully coalesced row segments.
-    const int q = warp & 3;                              // TMEM lane quadrant this warp may touch
-    float* stage = stage_base + q * (32 * 33);
-    long long* row_out = rowoff_base + q * 64;           // [32] output row offsets (or -1), [32] residual offsets
-    long long* row_res = row_out + 32;
+    // ------------------------------------------------------------ epilogue (8 warps: TMEM quadrant x column half)
+    // TMEM hands every thread one output ROW.  Arithmetic (bias, residual, activation) is done in that layout;
+    // global traffic goes through a per-warp padded smem tile (32 rows x 64 B) so that every LDG/STG of a warp
+    // covers whole 64-byte row segments (4 lanes x 16 B per row) instead of 32 different cache lines.
+    const int e = warp - kEpiWarp0;
+    const int q = e & 3, half = e >> 2;                  // TMEM lane quadrant (== warp % 4) and column half
+    uint8_t* tile = tile_s[e];                           // [32][kTilePitch] bytes
+    long long* row_out = rowoff_s[e];                    // [32] output row offsets (or -1), [32] residual offsets
+    long long* row_res = rowoff_s[e] + 32;
     int acc = 0; uint32_t acc_phase = 0;
     const bool row_major = (p.ocs == 1);
-    for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-      const int m0 = (tile / p.N_tiles) * BM, n0 = (tile % p.N_tiles) * BN;
+    const bool gate = (p.act == PT_ACT_GATE);
+    const int pr = lane >> 2, pc = lane & 3;             // piece mapping: row pr + 8*j, 16-byte piece pc
+    for (int tile_i = blockIdx.x; tile_i < n_tiles_total; tile_i += gridDim.x) {
+      const int m0 = (tile_i / p.N_tiles) * BM, n0 = (tile_i % p.N_tiles) * BN;
       const int m = m0 + q * 32 + lane;
       const int b = m / p.rows_per_sample, t = m - b * p.rows_per_sample;
       const bool row_ok = (m < p.M) && (t < p.t_valid);
       const long long obase = (long long)b * p.oss + (long long)t * p.ors;
-      const long long rbase = (long long)b * p.rss + (long long)t * p.rrs;
       __syncwarp();
       row_out[lane] = row_ok ? obase : -1;
-      row_res[lane] = rbase;
+      row_res[lane] = (long long)b * p.rss + (long long)t * p.rrs;
       __syncwarp();
       pt::mbar_wait(&tmem_full[acc], acc_phase);
       pt::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
         const int n = n0 + c0;
         if (n >= p.n_valid) break;                       // warp-uniform
         uint32_t v[32];
         pt::tmem_ld32(t_row + c0, v);
         pt::tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+        if (p.bias) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n) + i);
+            f[4 * i] += bb.x; f[4 * i + 1] += bb.y; f[4 * i + 2] += bb.z; f[4 * i + 3] += bb.w;
+          }
+        }
         if (!row_major) {
           // channel-major output (final projections): lanes = consecutive rows -> already coalesced per column
           if (row_ok) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
               if (n + i < p.n_valid) {
-                float f = __uint_as_float(v[i]) + (p.bias ? __ldg(p.bias + n + i) : 0.f);
-                f = apply_act(f, p.act, p.slope);
+                const float x = apply_act(f[i], p.act, p.slope);
                 const long long off = obase + (long long)(n + i) * p.ocs;
-                if (p.out_f32) static_cast<float*>(p.out)[off] = f;
-                else static_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(f);
+                if (p.out_f32) static_cast<float*>(p.out)[off] = x;
+                else static_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(x);
               }
             }
           }
           continue;
         }
-        __syncwarp();
+        // ---- residual: coalesced 64-byte row segments -> smem tile -> own row
+        if (p.residual) {
+          if (p.res_f32) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) stage[lane * 33 + i] = __uint_as_float(v[i]);
-        __syncwarp();
-        if (p.act == PT_ACT_GATE) {
-          // interleaved columns (a0,b0,a1,b1,...): even lanes tanh(a), odd lanes sigmoid(b), product on even lanes
-          const float bv = p.bias ? __ldg(p.bias + n + lane) : 0.f;
-          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(p.out) + ((n + lane) >> 1);
-#pragma unroll 4
-          for (int rr = 0; rr < 32; ++rr) {
-            const float x = stage[rr * 33 + lane] + bv;
-            const float f = (lane & 1) ? 1.f / (1.f + __expf(-x)) : tanhf(x);
-            const float pr = f * __shfl_xor_sync(0xffffffffu, f, 1);
-            const float pr2 = __shfl_down_sync(0xffffffffu, pr, 2);
+            for (int h2 = 0; h2 < 2; ++h2) {             // 16 fp32 columns (64 B) at a time
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int rr = pr + 8 * j;
+                float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row_out[rr] >= 0 && n + h2 * 16 + pc * 4 < p.n_valid)
+                  x = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + row_res[rr] + n + h2 * 16) + pc);
+                *reinterpret_cast<float4*>(tile + rr * kTilePitch + pc * 16) = x;
+              }
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 x = *reinterpret_cast<const float4*>(tile + lane * kTilePitch + i * 16);
+                f[h2 * 16 + 4 * i] += x.x; f[h2 * 16 + 4 * i + 1] += x.y; f[h2 * 16 + 4 * i + 2] += x.z; f[h2 * 16 + 4 * i + 3] += x.w;
+              }
+            }
+          } else {
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int rr = pr + 8 * j;
+              uint4 x = make_uint4(0, 0, 0, 0);
+              if (row_out[rr] >= 0 && n + pc * 8 < p.n_valid)
+                x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + row_res[rr] + n) + pc);
+              *reinterpret_cast<uint4*>(tile + rr * kTilePitch + pc * 16) = x;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint4 x = *reinterpret_cast<const uint4*>(tile + lane * kTilePitch + i * 16);
+              const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&w4[j]);
+                f[8 * i + 2 * j] += __bfloat162float(hh.x);
+                f[8 * i + 2 * j + 1] += __bfloat162float(hh.y);
+              }
+            }
+          }
+        }
+        // ---- activation + store through the tile
+        if (gate) {
+          // interleaved columns (a0,b0,a1,b1,...) -> tanh(a) * sigmoid(b): 16 bf16 outputs (32 B) per row
+          uint32_t g8[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float g0 = tanhf(f[4 * i]) * (1.f / (1.f + __expf(-f[4 * i + 1])));
+            const float g1 = tanhf(f[4 * i + 2]) * (1.f / (1.f + __expf(-f[4 * i + 3])));
+            g8[i] = pt::pack_bf16x2(g0, g1);
+          }
+          __syncwarp();
+          *reinterpret_cast<uint4*>(tile + lane * kTilePitch) = make_uint4(g8[0], g8[1], g8[2], g8[3]);
+          *reinterpret_cast<uint4*>(tile + lane * kTilePitch + 16) = make_uint4(g8[4], g8[5], g8[6], g8[7]);
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int rr = (lane >> 1) + 16 * j, pp = lane & 1;
             const long long ro = row_out[rr];
-            if (ro >= 0 && (lane & 3) == 0) *reinterpret_cast<uint32_t*>(o + ro) = pt::pack_bf16x2(pr, pr2);
+            if (ro >= 0)
+              *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + (n >> 1) + pp * 8) =
+                  *reinterpret_cast<const uint4*>(tile + rr * kTilePitch + pp * 16);
           }
         } else if (p.out_f32) {
-          // one lane per column, one row per iteration: 128 B stores
-          const int col = n + lane;
-          const bool col_ok = col < p.n_valid;
-          const float bv = (p.bias && col_ok) ? __ldg(p.bias + col) : 0.f;
-          float* o = static_cast<float*>(p.out) + col;
-#pragma unroll 8
-          for (int rr = 0; rr < 32; ++rr) {
-            const long long ro = row_out[rr];
-            float x = stage[rr * 33 + lane] + bv;
-            if (ro >= 0 && col_ok) {
-              if (p.residual) {
-                x += p.res_f32 ? __ldg(static_cast<const float*>(p.residual) + row_res[rr] + col)
-                               : __bfloat162float(static_cast<const __nv_bfloat16*>(p.residual)[row_res[rr] + col]);
-              }
-              o[ro] = apply_act(x, p.act, p.slope);
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<float4*>(tile + lane * kTilePitch + i * 16) =
+                  make_float4(apply_act(f[h2 * 16 + 4 * i], p.act, p.slope), apply_act(f[h2 * 16 + 4 * i + 1], p.act, p.slope),
+                              apply_act(f[h2 * 16 + 4 * i + 2], p.act, p.slope), apply_act(f[h2 * 16 + 4 * i + 3], p.act, p.slope));
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int rr = pr + 8 * j;
+              const long long ro = row_out[rr];
+              if (ro >= 0 && n + h2 * 16 + pc * 4 < p.n_valid)
+                *(reinterpret_cast<float4*>(static_cast<float*>(p.out) + ro + n + h2 * 16) + pc) =
+                    *reinterpret_cast<const float4*>(tile + rr * kTilePitch + pc * 16);
             }
           }
         } else {
-          // bf16 output: half a warp per row, two columns per lane: 64 B stores, two rows per iteration
-          const int hl = lane & 15, hr = lane >> 4;
-          const int col = n + 2 * hl;
-          const bool c0_ok = col < p.n_valid, c1_ok = col + 1 < p.n_valid;
-          const float b0 = (p.bias && c0_ok) ? __ldg(p.bias + col) : 0.f;
-          const float b1 = (p.bias && c1_ok) ? __ldg(p.bias + col + 1) : 0.f;
-          __nv_bfloat16* o = static_cast<__nv_bfloat16*>(p.out) + col;
-#pragma unroll 4
-          for (int r2 = 0; r2 < 32; r2 += 2) {
-            const int rr = r2 + hr;
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(tile + lane * kTilePitch + i * 16) = make_uint4(
+                pt::pack_bf16x2(apply_act(f[8 * i], p.act, p.slope), apply_act(f[8 * i + 1], p.act, p.slope)),
+                pt::pack_bf16x2(apply_act(f[8 * i + 2], p.act, p.slope), apply_act(f[8 * i + 3], p.act, p.slope)),
+                pt::pack_bf16x2(apply_act(f[8 * i + 4], p.act, p.slope), apply_act(f[8 * i + 5], p.act, p.slope)),
+                pt::pack_bf16x2(apply_act(f[8 * i + 6], p.act, p.slope), apply_act(f[8 * i + 7], p.act, p.slope)));
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int rr = pr + 8 * j;
             const long long ro = row_out[rr];
-            float x0 = stage[rr * 33 + 2 * hl] + b0, x1 = stage[rr * 33 + 2 * hl + 1] + b1;
-            if (ro >= 0 && c0_ok) {
-              if (p.residual) {
-                if (p.res_f32) {
-                  const float* r = static_cast<const float*>(p.residual) + row_res[rr] + col;
-                  x0 += __ldg(r);
-                  if (c1_ok) x1 += __ldg(r + 1);
-                } else {
-                  const __nv_bfloat16* r = static_cast<const __nv_bfloat16*>(p.residual) + row_res[rr] + col;
-                  x0 += __bfloat162float(r[0]);
-                  if (c1_ok) x1 += __bfloat162float(r[1]);
-                }
-              }
-              x0 = apply_act(x0, p.act, p.slope);
-              x1 = apply_act(x1, p.act, p.slope);
-              if (c1_ok) *reinterpret_cast<uint32_t*>(o + ro) = pt::pack_bf16x2(x0, x1);
-              else o[ro] = __float2bfloat16_rn(x0);
-            }
+            if (ro >= 0 && n + pc * 8 < p.n_valid)
+              *(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + n) + pc) =
+                  *reinterpret_cast<const uint4*>(tile + rr * kTilePitch + pc * 16);
           }
         }
       }
@@ -337,6 +388,21 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     return pt::fail("pt_gemm_bf16: gated epilogue needs bf16 row-major output, no residual, n_valid %% 32 == 0");
   if ((reinterpret_cast<uintptr_t>(d->a) | reinterpret_cast<uintptr_t>(d->w)) & 15)
     return pt::fail("pt_gemm_bf16: operands must be 16-byte aligned");
+  if (d->bias && (reinterpret_cast<uintptr_t>(d->bias) & 15)) return pt::fail("pt_gemm_bf16: bias must be 16-byte aligned");
+  if (d->ocs == 1) {
+    // row-major outputs / residuals move in 16-byte pieces
+    const int vec = d->out_f32 ? 4 : 8;
+    const int nv = d->act == PT_ACT_GATE ? d->n_valid / 2 : d->n_valid;
+    if ((nv % vec) || (d->ors % vec) || (d->oss % vec) || (reinterpret_cast<uintptr_t>(d->out) & 15))
+      return pt::fail("pt_gemm_bf16: row-major output needs n_valid, strides and base aligned to 16 bytes");
+    if (d->residual) {
+      const int rvec = d->res_f32 ? 4 : 8;
+      if ((d->n_valid % rvec) || (d->rrs % rvec) || (d->rss % rvec) || (reinterpret_cast<uintptr_t>(d->residual) & 15))
+        return pt::fail("pt_gemm_bf16: residual needs n_valid, strides and base aligned to 16 bytes");
+    }
+  } else if (d->residual) {
+    return pt::fail("pt_gemm_bf16: a residual needs a row-major output");
+  }
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

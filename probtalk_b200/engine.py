@@ -423,15 +423,16 @@ class StackWeights:
 class StackPlanner:
     """Records the launches of a 6-layer DeepSupervisionLayer stack over fixed buffers.
 
-    x32 / xb : fp32 master + bf16 copy of the residual stream [B*N, 512]
-    memb     : bf16 memory rows [B*Mem, 512]; labels int32 [B]."""
+    xb   : the residual stream [B*N, 512] in bf16 (every sub-block ends in a LayerNorm, so rounding does not
+           accumulate across layers); r: pre-norm sum x + style(...) in bf16; LayerNorm statistics are fp32
+    memb : bf16 memory rows [B*Mem, 512]; labels int32 [B]."""
 
     def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device):
         self.p, self.W, self.B, self.N, self.Mem = plan, W, B, N, Mem
         M = B * N
         self.M = M
         z = lambda *s, dt=BF16: torch.zeros(*s, dtype=dt, device=device)
-        self.x32, self.xb = z(M, D_MODEL, dt=F32), z(M, D_MODEL)
+        self.xb = z(M, D_MODEL)
         self.memb = z(B * Mem, D_MODEL)
         self.kv = z(B * Mem, 2 * D_MODEL * len(W.layers))
         self.qkv = z(M, 3 * D_MODEL)
@@ -439,7 +440,7 @@ class StackPlanner:
         self.att = z(M, D_MODEL)
         self.proj = z(M, D_MODEL)
         self.sil = z(M, D_MODEL)
-        self.r32 = z(M, D_MODEL, dt=F32)
+        self.r = z(M, D_MODEL)
         self.ff = z(M, 4 * D_MODEL)
         self.labels = labels
 
@@ -453,9 +454,9 @@ class StackPlanner:
         p, M = self.p, self.M
         p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
                self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
-        p.linear(self.sil, M, st.out, self.r32, residual=self.x32, rss=0, rrs=D_MODEL, rows_per_sample=None)
+        p.linear(self.sil, M, st.out, self.r, residual=self.xb, rss=0, rrs=D_MODEL, rows_per_sample=None)
         g, b = lw.norms[i]
-        p.call(L.pt_layernorm512, self.r32.data_ptr(), g.data_ptr(), b.data_ptr(), self.x32.data_ptr(), self.xb.data_ptr(), M)
+        p.call(L.pt_layernorm512, self.r.data_ptr(), 0, g.data_ptr(), b.data_ptr(), None, self.xb.data_ptr(), M)
 
     def record_layers(self):
         L = _lib.lib()
@@ -622,7 +623,7 @@ class PredictorPlan:
         self.cur = torch.full((B, self.N), MASK_ID, dtype=torch.int32, device=dev)
         self.bad = torch.zeros(1, dtype=torch.int32, device=dev)
         pb.call(L.pt_embed_tokens512, self.cur.data_ptr(), PW.tok_emb.data_ptr(), PW.n_emb, self.x_pe64.data_ptr(), self.N,
-                self.stack.x32.data_ptr(), self.stack.xb.data_ptr(), M, self.bad.data_ptr())
+                None, self.stack.xb.data_ptr(), M, self.bad.data_ptr())
         self.stack.record_layers()
         self.h1 = torch.zeros(M, D_MODEL, dtype=BF16, device=dev)
         self.logits = torch.zeros(M, PW.n_codes, dtype=F32, device=dev)
@@ -734,7 +735,6 @@ class RefinerPlan:
         self.stack = StackPlanner(p, RW.stack, B, T, T, self.labels, dev)
         st = self.stack
         # x = float32(input_conv(blank) + PE)   (RTransformer.py:211-214)
-        p.linear(xin.t, M, RW.input_conv, st.x32, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
         p.linear(xin.t, M, RW.input_conv, st.xb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
         p.linear(xc.t, M, RW.audio_conv, st.memb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
         st.record_memory_kv()
