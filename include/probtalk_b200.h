@@ -118,10 +118,11 @@ int pt_pack_mask(const float* mask, void* dst_bf16, int B, int T, int Tp, int H,
 int pt_interp_blend(const float* known, const float* mask, const float* pred, int pred_T, float* out, int B, int C,
                     int T, int mask_pow, void* stream);
 
-/* nn.LayerNorm(512, eps 1e-5) over rows (norm1/2/3, PTransformer.py:329-331): fp32 or bf16 in (fp32 statistics),
+/* out = LayerNorm512(in + residual), eps 1e-5: the `x = norm_i(x + sublayer(x))` of the post-norm layer
+ * (PTransformer.py:329-331).  in fp32 or bf16, residual bf16 or NULL (may alias out_bf16), fp32 statistics,
  * fp32 and/or bf16 out. */
-int pt_layernorm512(const void* in, int in_f32, const float* gamma, const float* beta, float* out_f32, void* out_bf16,
-                    int M, void* stream);
+int pt_layernorm512(const void* in, int in_f32, const void* residual_bf16, const float* gamma, const float* beta,
+                    float* out_f32, void* out_bf16, int M, void* stream);
 
 /* StylizationBlock_V3 'sb' branch before its output Linear (PTransformer.py:134-139):
  *   out = SiLU( LN(in) * (1 + scale) + shift ),  [scale | shift] = mod[labels[row / rows_per_sample]]  (mod: [n_classes, 1024] fp32,

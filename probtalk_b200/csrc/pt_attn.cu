@@ -4,7 +4,7 @@
 // (reference nets/inpainting/PTransformer.py:340 self-attention, :350 cross-attention): 8 heads x 64,
 // no masks, softmax over all keys.  Sequences on this path are tiny (88 tokens x 22 memory steps for the
 // predictor, 180 x 180 for the refiner), so one CTA owns one (sample, head): K, V and Q live in shared
-// memory, each warp owns 16-query blocks and walks the keys in blocks of 64 with an online softmax.
+// memory, each warp owns 16-query blocks and walks the keys in blocks of 32 with an online softmax.
 // Tensor-core work uses warp-level mma.sync m16n8k16 (bf16 in, fp32 accumulate): at <= 192 keys per head a
 // 128-row tcgen05 tile would be mostly padding; attention is < 10 % of the path's FLOPs.
 #include "pt_common.cuh"
@@ -37,135 +37,179 @@ struct AttnArgs {
   float scale_log2e;
 };
 
-// Keys are processed in blocks of 64 with an online softmax (running max / sum, accumulator rescale), so the
-// register footprint is independent of the sequence length and several CTAs fit on an SM.
-constexpr int kKeyBlock = 64;
+// Persistent CTAs walk (sample, head) pairs; the next pair's K, V and Q are prefetched with cp.async into the
+// second half of a double-buffered smem tile while the tensor cores work on the current one.  Keys are processed
+// in blocks of 32 with an online softmax (running max / sum, accumulator rescale), so the register footprint is
+// independent of the sequence length.
+constexpr int kKeyBlock = 32;
 
-__global__ void __launch_bounds__(kWarps * 32, 2) attention_kernel(AttnArgs a) {
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, bool valid) {
+  const uint32_t d = pt::smem_u32(smem_dst);
+  const int sz = valid ? 16 : 0;                          // src-size 0 -> 16 bytes of zeros
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(kWarps * 32, 2) attention_kernel(AttnArgs a, int n_pairs, int nbuf) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int NKP = ((a.Nk + kKeyBlock - 1) / kKeyBlock) * kKeyBlock;
-  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw);
-  __nv_bfloat16* Vs = Ks + NKP * kRowPad;
-  __nv_bfloat16* Qs = Vs + NKP * kRowPad;
-  const int b = blockIdx.x / a.heads, h = blockIdx.x % a.heads;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int NQP = (a.Nq + 15) & ~15;
+  const int buf_elems = (2 * NKP + NQP) * kRowPad;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  // ---- stage K, V (zero-padded to NKP keys) and Q (zero-padded to NQP rows): 16-byte chunks, 8 per row
-  const __nv_bfloat16* kg = a.k + (size_t)b * a.Nk * a.k_stride + h * kHeadDim;
-  const __nv_bfloat16* vg = a.v + (size_t)b * a.Nk * a.v_stride + h * kHeadDim;
-  const __nv_bfloat16* qg = a.q + (size_t)b * a.Nq * a.q_stride + h * kHeadDim;
-  for (int i = tid; i < NKP * 8; i += kWarps * 32) {
-    const int r = i >> 3, c = (i & 7) * 8;
-    uint4 kv = make_uint4(0, 0, 0, 0), vv = kv;
-    if (r < a.Nk) {
-      kv = __ldg(reinterpret_cast<const uint4*>(kg + (size_t)r * a.k_stride + c));
-      vv = __ldg(reinterpret_cast<const uint4*>(vg + (size_t)r * a.v_stride + c));
+  auto stage = [&](int pair, int buf) {
+    __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw) + (size_t)buf * buf_elems;
+    __nv_bfloat16* Vs = Ks + NKP * kRowPad;
+    __nv_bfloat16* Qs = Vs + NKP * kRowPad;
+    const int b = pair / a.heads, h = pair % a.heads;
+    const __nv_bfloat16* kg = a.k + (size_t)b * a.Nk * a.k_stride + h * kHeadDim;
+    const __nv_bfloat16* vg = a.v + (size_t)b * a.Nk * a.v_stride + h * kHeadDim;
+    const __nv_bfloat16* qg = a.q + (size_t)b * a.Nq * a.q_stride + h * kHeadDim;
+    for (int i = tid; i < NKP * 8; i += kWarps * 32) {
+      const int r = i >> 3, c = (i & 7) * 8;
+      const bool ok = r < a.Nk;
+      const size_t rr = ok ? r : 0;
+      cp_async16(Ks + r * kRowPad + c, kg + rr * a.k_stride + c, ok);
+      cp_async16(Vs + r * kRowPad + c, vg + rr * a.v_stride + c, ok);
     }
-    *reinterpret_cast<uint4*>(Ks + r * kRowPad + c) = kv;
-    *reinterpret_cast<uint4*>(Vs + r * kRowPad + c) = vv;
-  }
-  for (int i = tid; i < NQP * 8; i += kWarps * 32) {
-    const int r = i >> 3, c = (i & 7) * 8;
-    uint4 qv = make_uint4(0, 0, 0, 0);
-    if (r < a.Nq) qv = __ldg(reinterpret_cast<const uint4*>(qg + (size_t)r * a.q_stride + c));
-    *reinterpret_cast<uint4*>(Qs + r * kRowPad + c) = qv;
-  }
-  __syncthreads();
+    for (int i = tid; i < NQP * 8; i += kWarps * 32) {
+      const int r = i >> 3, c = (i & 7) * 8;
+      const bool ok = r < a.Nq;
+      cp_async16(Qs + r * kRowPad + c, qg + (size_t)(ok ? r : 0) * a.q_stride + c, ok);
+    }
+  };
 
+  int pair = blockIdx.x;
+  if (pair < n_pairs) stage(pair, 0);
+  cp_async_commit();
   const int g = lane >> 2, tig = lane & 3;
-  for (int qb = warp; qb * 16 < a.Nq; qb += kWarps) {
-    uint32_t qf[4][4];
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks) {
-      const __nv_bfloat16* q0 = Qs + (qb * 16 + g) * kRowPad + ks * 16 + tig * 2;
-      qf[ks][0] = *reinterpret_cast<const uint32_t*>(q0);
-      qf[ks][1] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kRowPad);
-      qf[ks][2] = *reinterpret_cast<const uint32_t*>(q0 + 8);
-      qf[ks][3] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kRowPad + 8);
+  for (int it = 0; pair < n_pairs; pair += gridDim.x, ++it) {
+    const int buf = (nbuf == 2) ? (it & 1) : 0;
+    const int next = pair + gridDim.x;
+    if (nbuf == 2) {
+      if (next < n_pairs) stage(next, buf ^ 1);          // the other buffer was released by the barrier below
+      cp_async_commit();
+      cp_async_wait<1>();                                // this pair's group has landed (the newest may be in flight)
+    } else {
+      cp_async_wait<0>();
     }
-    float mx0 = -INFINITY, mx1 = -INFINITY, sum0 = 0.f, sum1 = 0.f;
-    float oacc[8][4];
-#pragma unroll
-    for (int nt = 0; nt < 8; ++nt) oacc[nt][0] = oacc[nt][1] = oacc[nt][2] = oacc[nt][3] = 0.f;
+    __syncthreads();
+    const __nv_bfloat16* Ks = reinterpret_cast<const __nv_bfloat16*>(smem_raw) + (size_t)buf * buf_elems;
+    const __nv_bfloat16* Vs = Ks + NKP * kRowPad;
+    const __nv_bfloat16* Qs = Vs + NKP * kRowPad;
+    const int b = pair / a.heads, h = pair % a.heads;
 
-    for (int kb = 0; kb < NKP; kb += kKeyBlock) {
-      // S = Q K^T for 64 keys: 8 tiles of 8 keys
-      float sacc[8][4];
+    for (int qb = warp; qb * 16 < a.Nq; qb += kWarps) {
+      uint32_t qf[4][4];
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
+      for (int ks = 0; ks < 4; ++ks) {
+        const __nv_bfloat16* q0 = Qs + (qb * 16 + g) * kRowPad + ks * 16 + tig * 2;
+        qf[ks][0] = *reinterpret_cast<const uint32_t*>(q0);
+        qf[ks][1] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kRowPad);
+        qf[ks][2] = *reinterpret_cast<const uint32_t*>(q0 + 8);
+        qf[ks][3] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kRowPad + 8);
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY, sum0 = 0.f, sum1 = 0.f;
+      float oacc[8][4];
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {
-          const __nv_bfloat16* kp = Ks + (kb + nt * 8 + g) * kRowPad + ks * 16 + tig * 2;
-          mma_bf16(sacc[nt], qf[ks], *reinterpret_cast<const uint32_t*>(kp), *reinterpret_cast<const uint32_t*>(kp + 8));
+      for (int nt = 0; nt < 8; ++nt) oacc[nt][0] = oacc[nt][1] = oacc[nt][2] = oacc[nt][3] = 0.f;
+
+      for (int kb = 0; kb < NKP; kb += kKeyBlock) {
+        // S = Q K^T for 32 keys: 4 tiles of 8 keys
+        float sacc[4][4];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            const __nv_bfloat16* kp = Ks + (kb + nt * 8 + g) * kRowPad + ks * 16 + tig * 2;
+            mma_bf16(sacc[nt], qf[ks], *reinterpret_cast<const uint32_t*>(kp), *reinterpret_cast<const uint32_t*>(kp + 8));
+          }
+        }
+        float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          const int key = kb + nt * 8 + tig * 2;
+          if (key >= a.Nk) { sacc[nt][0] = -INFINITY; sacc[nt][2] = -INFINITY; }
+          if (key + 1 >= a.Nk) { sacc[nt][1] = -INFINITY; sacc[nt][3] = -INFINITY; }
+          bm0 = fmaxf(bm0, fmaxf(sacc[nt][0], sacc[nt][1]));
+          bm1 = fmaxf(bm1, fmaxf(sacc[nt][2], sacc[nt][3]));
+        }
+        bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1)); bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+        bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1)); bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+        const float nm0 = fmaxf(mx0, bm0), nm1 = fmaxf(mx1, bm1);     // finite: every block holds at least one valid key
+        const float sc0 = exp2f((mx0 - nm0) * a.scale_log2e), sc1 = exp2f((mx1 - nm1) * a.scale_log2e);
+        mx0 = nm0; mx1 = nm1;
+        sum0 *= sc0; sum1 *= sc1;
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) { oacc[nt][0] *= sc0; oacc[nt][1] *= sc0; oacc[nt][2] *= sc1; oacc[nt][3] *= sc1; }
+        uint32_t pf[4][2];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          const float p0 = exp2f((sacc[nt][0] - mx0) * a.scale_log2e), p1 = exp2f((sacc[nt][1] - mx0) * a.scale_log2e);
+          const float p2 = exp2f((sacc[nt][2] - mx1) * a.scale_log2e), p3 = exp2f((sacc[nt][3] - mx1) * a.scale_log2e);
+          sum0 += p0 + p1; sum1 += p2 + p3;
+          pf[nt][0] = pt::pack_bf16x2(p0, p1);
+          pf[nt][1] = pt::pack_bf16x2(p2, p3);
+        }
+        // O += P V for this key block (two 16-key steps)
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) {
+          const uint32_t af[4] = {pf[2 * kt][0], pf[2 * kt][1], pf[2 * kt + 1][0], pf[2 * kt + 1][1]};
+#pragma unroll
+          for (int np = 0; np < 4; ++np) {
+            uint32_t bf[4];
+            // lanes 0-7: keys +0..7 @ dim np*16 ; 8-15: keys +8..15 ; 16-23: keys +0..7 @ dim np*16+8 ; 24-31: keys +8..15
+            const __nv_bfloat16* vp = Vs + (kb + kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * kRowPad + np * 16 + (lane >> 4) * 8;
+            ldmatrix_x4_trans(bf, vp);
+            mma_bf16(oacc[2 * np], af, bf[0], bf[1]);
+            mma_bf16(oacc[2 * np + 1], af, bf[2], bf[3]);
+          }
         }
       }
-      float bm0 = -INFINITY, bm1 = -INFINITY;
+      sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+      sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+      const float inv0 = 1.f / sum0, inv1 = 1.f / sum1;
+      const int r0 = qb * 16 + g, r1 = r0 + 8;
+      __nv_bfloat16* o0 = a.out + ((size_t)b * a.Nq + r0) * a.out_stride + h * kHeadDim + tig * 2;
+      __nv_bfloat16* o1 = a.out + ((size_t)b * a.Nq + r1) * a.out_stride + h * kHeadDim + tig * 2;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        const int key = kb + nt * 8 + tig * 2;
-        if (key >= a.Nk) { sacc[nt][0] = -INFINITY; sacc[nt][2] = -INFINITY; }
-        if (key + 1 >= a.Nk) { sacc[nt][1] = -INFINITY; sacc[nt][3] = -INFINITY; }
-        bm0 = fmaxf(bm0, fmaxf(sacc[nt][0], sacc[nt][1]));
-        bm1 = fmaxf(bm1, fmaxf(sacc[nt][2], sacc[nt][3]));
-      }
-      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1)); bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
-      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1)); bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
-      const float nm0 = fmaxf(mx0, bm0), nm1 = fmaxf(mx1, bm1);       // finite: the first block always has a valid key
-      const float sc0 = exp2f((mx0 - nm0) * a.scale_log2e), sc1 = exp2f((mx1 - nm1) * a.scale_log2e);
-      mx0 = nm0; mx1 = nm1;
-      sum0 *= sc0; sum1 *= sc1;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) { oacc[nt][0] *= sc0; oacc[nt][1] *= sc0; oacc[nt][2] *= sc1; oacc[nt][3] *= sc1; }
-      uint32_t pf[8][2];
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        const float p0 = exp2f((sacc[nt][0] - mx0) * a.scale_log2e), p1 = exp2f((sacc[nt][1] - mx0) * a.scale_log2e);
-        const float p2 = exp2f((sacc[nt][2] - mx1) * a.scale_log2e), p3 = exp2f((sacc[nt][3] - mx1) * a.scale_log2e);
-        sum0 += p0 + p1; sum1 += p2 + p3;
-        pf[nt][0] = pt::pack_bf16x2(p0, p1);
-        pf[nt][1] = pt::pack_bf16x2(p2, p3);
-      }
-      // O += P V for this key block
-#pragma unroll
-      for (int kt = 0; kt < 4; ++kt) {
-        const uint32_t af[4] = {pf[2 * kt][0], pf[2 * kt][1], pf[2 * kt + 1][0], pf[2 * kt + 1][1]};
-#pragma unroll
-        for (int np = 0; np < 4; ++np) {
-          uint32_t bf[4];
-          // lanes 0-7: keys +0..7 @ dim np*16 ; 8-15: keys +8..15 ; 16-23: keys +0..7 @ dim np*16+8 ; 24-31: keys +8..15
-          const __nv_bfloat16* vp = Vs + (kb + kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * kRowPad + np * 16 + (lane >> 4) * 8;
-          ldmatrix_x4_trans(bf, vp);
-          mma_bf16(oacc[2 * np], af, bf[0], bf[1]);
-          mma_bf16(oacc[2 * np + 1], af, bf[2], bf[3]);
-        }
+        if (r0 < a.Nq) *reinterpret_cast<uint32_t*>(o0 + nt * 8) = pt::pack_bf16x2(oacc[nt][0] * inv0, oacc[nt][1] * inv0);
+        if (r1 < a.Nq) *reinterpret_cast<uint32_t*>(o1 + nt * 8) = pt::pack_bf16x2(oacc[nt][2] * inv1, oacc[nt][3] * inv1);
       }
     }
-    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
-    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
-    const float inv0 = 1.f / sum0, inv1 = 1.f / sum1;
-    const int r0 = qb * 16 + g, r1 = r0 + 8;
-    __nv_bfloat16* o0 = a.out + ((size_t)b * a.Nq + r0) * a.out_stride + h * kHeadDim + tig * 2;
-    __nv_bfloat16* o1 = a.out + ((size_t)b * a.Nq + r1) * a.out_stride + h * kHeadDim + tig * 2;
-#pragma unroll
-    for (int nt = 0; nt < 8; ++nt) {
-      if (r0 < a.Nq) *reinterpret_cast<uint32_t*>(o0 + nt * 8) = pt::pack_bf16x2(oacc[nt][0] * inv0, oacc[nt][1] * inv0);
-      if (r1 < a.Nq) *reinterpret_cast<uint32_t*>(o1 + nt * 8) = pt::pack_bf16x2(oacc[nt][2] * inv1, oacc[nt][3] * inv1);
+    __syncthreads();                                     // everyone is done with `buf` before it is refilled
+    if (nbuf == 1) {                                     // single buffer (very long sequences): no overlap
+      if (next < n_pairs) stage(next, 0);
+      cp_async_commit();
     }
   }
+  cp_async_wait<0>();
 }
 
 int launch_attn(const AttnArgs& a, int B, cudaStream_t st) {
   const int NQP = (a.Nq + 15) & ~15;
   const int NKP = ((a.Nk + kKeyBlock - 1) / kKeyBlock) * kKeyBlock;
-  const size_t smem = (size_t)(2 * NKP + NQP) * kRowPad * sizeof(__nv_bfloat16);
+  const size_t one = (size_t)(2 * NKP + NQP) * kRowPad * sizeof(__nv_bfloat16);
+  const int nbuf = (2 * one <= 226 * 1024) ? 2 : 1;
+  const size_t smem = nbuf * one;
+  if (smem > 226 * 1024) return pt::fail("pt_attention: Nq=%d Nk=%d do not fit in shared memory", a.Nq, a.Nk);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
     PT_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  attention_kernel<<<B * a.heads, kWarps * 32, smem, st>>>(a);
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int per_sm = (int)((227 * 1024) / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);   // __launch_bounds__(192, 2)
+  const int n_pairs = B * a.heads;
+  const int grid = n_pairs < sms * per_sm ? n_pairs : sms * per_sm;
+  attention_kernel<<<grid, kWarps * 32, smem, st>>>(a, n_pairs, nbuf);
   PT_CUDA(cudaGetLastError());
   return 0;
 }

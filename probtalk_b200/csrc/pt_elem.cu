@@ -133,13 +133,20 @@ __device__ __forceinline__ void ln_stats(const float (&v)[16], float& mean, floa
 
 // nn.LayerNorm (norm1/2/3 of DeepSupervisionLayer, PTransformer.py:329-331): fp32 in -> fp32 and/or bf16 out
 template <typename InT>
-__global__ void ln_kernel(const InT* __restrict__ in, const float* __restrict__ gamma, const float* __restrict__ beta,
+__global__ void ln_kernel(const InT* __restrict__ in, const __nv_bfloat16* __restrict__ res,
+                          const float* __restrict__ gamma, const float* __restrict__ beta,
                           float* __restrict__ out32, __nv_bfloat16* __restrict__ out16, int M) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
   float v[16];
   load_row16(in + (size_t)row * kDModel, lane, v);
+  if (res) {                                   // x + sublayer(x): the residual add of the post-norm layer
+    float r[16];
+    load_row16(res + (size_t)row * kDModel, lane, r);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] += r[i];
+  }
   float mean, rstd;
   ln_stats(v, mean, rstd);
 #pragma unroll
@@ -317,14 +324,15 @@ extern "C" int pt_interp_blend(const float* known, const float* mask, const floa
   return 0;
 }
 
-extern "C" int pt_layernorm512(const void* in, int in_f32, const float* gamma, const float* beta, float* out_f32,
-                               void* out_bf16, int M, void* stream) {
+extern "C" int pt_layernorm512(const void* in, int in_f32, const void* residual_bf16, const float* gamma,
+                               const float* beta, float* out_f32, void* out_bf16, int M, void* stream) {
   if (M <= 0) return 0;
   if (!in || !gamma || !beta || (!out_f32 && !out_bf16)) return pt::fail("pt_layernorm512: null pointer");
+  const __nv_bfloat16* res = (const __nv_bfloat16*)residual_bf16;
   if (in_f32)
-    ln_kernel<float><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const float*)in, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
+    ln_kernel<float><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const float*)in, res, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
   else
-    ln_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
+    ln_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, res, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
   PT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -454,9 +454,11 @@ class StackPlanner:
         p, M = self.p, self.M
         p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
                self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
-        p.linear(self.sil, M, st.out, self.r, residual=self.xb, rss=0, rrs=D_MODEL, rows_per_sample=None)
+        p.linear(self.sil, M, st.out, self.r)
         g, b = lw.norms[i]
-        p.call(L.pt_layernorm512, self.r.data_ptr(), 0, g.data_ptr(), b.data_ptr(), None, self.xb.data_ptr(), M)
+        # the residual add rides in the LayerNorm pass (a row-local read) instead of the GEMM epilogue
+        p.call(L.pt_layernorm512, self.r.data_ptr(), 0, self.xb.data_ptr(), g.data_ptr(), b.data_ptr(), None,
+               self.xb.data_ptr(), M)
 
     def record_layers(self):
         L = _lib.lib()

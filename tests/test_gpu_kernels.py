@@ -133,11 +133,15 @@ def test_layernorm_kernels_and_embed():
     x = torch.randn(M, 512, device="cuda", generator=g) * 3 + 1
     gamma, beta = torch.rand(512, device="cuda", generator=g) + 0.5, torch.randn(512, device="cuda", generator=g)
     o32, o16 = torch.zeros(M, 512, device="cuda"), torch.zeros(M, 512, device="cuda", dtype=torch.bfloat16)
-    _lib.check(L.pt_layernorm512(x.data_ptr(), 1, gamma.data_ptr(), beta.data_ptr(), o32.data_ptr(), o16.data_ptr(), M, _st()))
+    _lib.check(L.pt_layernorm512(x.data_ptr(), 1, None, gamma.data_ptr(), beta.data_ptr(), o32.data_ptr(), o16.data_ptr(), M, _st()))
     xb16 = x.bfloat16()
     o16b = torch.zeros_like(o16)
-    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, gamma.data_ptr(), beta.data_ptr(), None, o16b.data_ptr(), M, _st()))
+    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, None, gamma.data_ptr(), beta.data_ptr(), None, o16b.data_ptr(), M, _st()))
     assert (o16b.float() - F.layer_norm(xb16.float(), (512,), gamma, beta, 1e-5)).abs().max() < 0.05
+    res16 = torch.randn(M, 512, device="cuda", generator=g).bfloat16()
+    acc = res16.clone()                       # residual aliases the output, like the engine's x = LN(x + s)
+    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, acc.data_ptr(), gamma.data_ptr(), beta.data_ptr(), None, acc.data_ptr(), M, _st()))
+    assert (acc.float() - F.layer_norm(xb16.float() + res16.float(), (512,), gamma, beta, 1e-5)).abs().max() < 0.05
     ref = F.layer_norm(x, (512,), gamma, beta, 1e-5)
     assert (o32 - ref).abs().max() < 2e-5 and (o16.float() - ref).abs().max() < 0.05
     # style modulation: labels per sample of 8 rows, 4 classes
