@@ -83,6 +83,17 @@ typedef struct pt_gemm_desc {
   int res_f32;
   int act;                /* PT_ACT_*; PT_ACT_GATE: columns interleaved (a0,b0,a1,b1..) -> tanh(a)*sigmoid(b) */
   float slope;            /* LeakyReLU slope */
+  /* fused row normalisation over a 512-wide output row (N must be 512, bf16 row-major output):
+   *   out = f( (v - mean(v)) * rstd(v) * norm_a[c] + norm_b[c] ),  v = A.W^T + bias (+ bf16 residual, which may
+   *   alias out),  eps 1e-5,
+   *   c = labels[row / label_rows] (labels NULL: c = 0);  row_norm 0 = off, 1 = SiLU, 2 = identity.
+   * row_norm 1 is StylizationBlock_V3's  SiLU(LN(h)(1+scale)+shift)  (PTransformer.py:134-139) with
+   * norm_a = gamma*(1+scale_c), norm_b = beta*(1+scale_c)+shift_c;  row_norm 2 is a plain nn.LayerNorm. */
+  int row_norm;
+  const float* norm_a;    /* fp32 [n_classes, 512] */
+  const float* norm_b;    /* fp32 [n_classes, 512] */
+  const int* labels;      /* int32 per sample or NULL */
+  int label_rows;
 } pt_gemm_desc;
 
 int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);

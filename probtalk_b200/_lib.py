@@ -28,6 +28,8 @@ class GemmDesc(C.Structure):
         ("out_f32", C.c_int), ("bias", C.c_void_p), ("residual", C.c_void_p),
         ("rss", C.c_longlong), ("rrs", C.c_longlong), ("res_f32", C.c_int), ("act", C.c_int),
         ("slope", C.c_float),
+        ("row_norm", C.c_int), ("norm_a", C.c_void_p), ("norm_b", C.c_void_p), ("labels", C.c_void_p),
+        ("label_rows", C.c_int),
     ]
 
 

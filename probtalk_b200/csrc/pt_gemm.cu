@@ -58,6 +58,12 @@ struct GemmKernelArgs {
   int act;                        // pt_gemm.h: PT_ACT_*
   float slope;
   int m_tiles;
+  // row-norm epilogue (cluster of 2 CTAs covers the 512-wide row): out = f( (v - mean) * rstd * A[c] + B[c] )
+  int row_norm;                   // 0 none, 1 SiLU, 2 identity
+  const float* norm_a;            // [n_classes, 512]
+  const float* norm_b;            // [n_classes, 512]
+  const int* labels;              // class per sample (row / label_rows) or null (class 0)
+  int label_rows;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act, float slope) {
@@ -66,7 +72,32 @@ __device__ __forceinline__ float apply_act(float v, int act, float slope) {
   return v;
 }
 
-template <int BN>
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_peer(const void* local_smem, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(pt::smem_u32(local_smem)), "r"(rank));
+  return r;
+}
+// Chan's parallel-variance merge of (n, mean, M2) partials
+__device__ __forceinline__ void welford_merge(float& n, float& mean, float& m2, float nb, float mb, float m2b) {
+  const float tot = n + nb, d = mb - mean;
+  mean += d * (nb / tot);
+  m2 += m2b + d * d * (n * nb / tot);
+  n = tot;
+}
+
+// kRowNorm: launched as clusters of two CTAs; CTA `rank` owns columns [rank*256, rank*256+256) of the same 128
+// rows, and the two exchange per-row (mean, M2) partials through distributed shared memory so that the epilogue can
+// apply a LayerNorm over the full 512-wide row (StylizationBlock_V3 / norm1-3 of the reference) in place.
+template <int BN, bool kRowNorm>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const GemmKernelArgs p) {
@@ -83,9 +114,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   // dynamic buffer lose their address space and become slow generic loads)
   __shared__ __align__(16) uint8_t tile_s[kEpiWarps][32 * kTilePitch];
   __shared__ long long rowoff_s[kEpiWarps][64];
+  __shared__ float2 stats_s[kRowNorm ? 2 : 1][4][kRowNorm ? BM : 1];    // [tile parity][source warp-column][row] (mean, M2)
+  __shared__ uint64_t stats_bar[2];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tiles_total = p.m_tiles * p.N_tiles;
+  const uint32_t rank = kRowNorm ? cluster_ctarank() : 0u;
+  const int tile_first = kRowNorm ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_stride = kRowNorm ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int n_tiles_total = kRowNorm ? p.m_tiles : p.m_tiles * p.N_tiles;
+  auto tile_m0 = [&](int tile) { return kRowNorm ? tile * BM : (tile / p.N_tiles) * BM; };
+  auto tile_n0 = [&](int tile) { return kRowNorm ? (int)rank * BN : (tile % p.N_tiles) * BN; };
 
   if (warp == 0 && lane == 0) {
     pt::tma_prefetch_desc(&tmap_a);
@@ -94,6 +132,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], kEpiWarps); }
+    if constexpr (kRowNorm) { pt::mbar_init(&stats_bar[0], 2 * kEpiWarps); pt::mbar_init(&stats_bar[1], 2 * kEpiWarps); }
     pt::fence_mbar_init();
   }
   if (warp == 2) {
@@ -103,14 +142,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   pt::tc_fence_before();
   __syncthreads();
   pt::tc_fence_after();
+  if constexpr (kRowNorm) cluster_sync_all();          // the peer's barriers exist before anyone arrives on them
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-        const int m0 = (tile / p.N_tiles) * BM, n0 = (tile % p.N_tiles) * BN;
+      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
+        const int m0 = tile_m0(tile), n0 = tile_n0(tile);
         for (int kk = 0; kk < p.K_iters; ++kk) {
           const int tap = kk / p.c_iters, cc = kk - tap * p.c_iters;
           pt::mbar_wait(&empty[stage], phase ^ 1);
@@ -128,7 +168,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const uint32_t idesc = pt::umma_idesc_bf16(BM, BN);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
         pt::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         pt::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -163,8 +203,33 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     const bool row_major = (p.ocs == 1);
     const bool gate = (p.act == PT_ACT_GATE);
     const int pr = lane >> 2, pc = lane & 3;             // piece mapping: row pr + 8*j, 16-byte piece pc
-    for (int tile_i = blockIdx.x; tile_i < n_tiles_total; tile_i += gridDim.x) {
-      const int m0 = (tile_i / p.N_tiles) * BM, n0 = (tile_i % p.N_tiles) * BN;
+    // f[0..31] += residual[row, n .. n+31] (bf16, row-major): coalesced 64-byte row segments -> smem tile -> own row
+    auto add_residual_bf16 = [&](float (&f)[32], int n) {
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int rr = pr + 8 * j;
+        uint4 x = make_uint4(0, 0, 0, 0);
+        if (row_out[rr] >= 0 && n + pc * 8 < p.n_valid)
+          x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + row_res[rr] + n) + pc);
+        *reinterpret_cast<uint4*>(tile + rr * kTilePitch + pc * 16) = x;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint4 x = *reinterpret_cast<const uint4*>(tile + lane * kTilePitch + i * 16);
+        const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&w4[j]);
+          f[8 * i + 2 * j] += __bfloat162float(hh.x);
+          f[8 * i + 2 * j + 1] += __bfloat162float(hh.y);
+        }
+      }
+    };
+    int it = 0;
+    for (int tile_i = tile_first; tile_i < n_tiles_total; tile_i += tile_stride, ++it) {
+      const int m0 = tile_m0(tile_i), n0 = tile_n0(tile_i);
       const int m = m0 + q * 32 + lane;
       const int b = m / p.rows_per_sample, t = m - b * p.rows_per_sample;
       const bool row_ok = (m < p.M) && (t < p.t_valid);
@@ -176,6 +241,115 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       pt::mbar_wait(&tmem_full[acc], acc_phase);
       pt::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      if constexpr (kRowNorm) {
+        // ---- pass 1: per-row statistics of this warp's 128 columns (Welford per 32-column chunk, Chan merge)
+        float wn = 0.f, wmean = 0.f, wm2 = 0.f;
+#pragma unroll 1
+        for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
+          const int n = n0 + c0;
+          uint32_t v[32];
+          pt::tmem_ld32(t_row + c0, v);
+          pt::tmem_ld_wait();
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n) + i);
+            f[4 * i] = __uint_as_float(v[4 * i]) + bb.x; f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + bb.y;
+            f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + bb.z; f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bb.w;
+          }
+          if (p.residual) add_residual_bf16(f, n);
+          float sum = 0.f;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) sum += f[i];
+          const float cm = sum * (1.f / 32.f);
+          float m2 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) { const float d = f[i] - cm; m2 = fmaf(d, d, m2); }
+          if (wn == 0.f) { wn = 32.f; wmean = cm; wm2 = m2; }
+          else welford_merge(wn, wmean, wm2, 32.f, cm, m2);
+        }
+        // ---- publish (mean, M2) to both CTAs of the pair, then wait for all four partials of every row
+        const int par = it & 1, src = (int)rank * 2 + half, row = q * 32 + lane;
+        stats_s[par][src][row] = make_float2(wmean, wm2);
+        const uint32_t peer = map_to_peer(&stats_s[par][src][row], rank ^ 1u);
+        asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(peer), "f"(wmean), "f"(wm2) : "memory");
+        asm volatile("fence.acq_rel.cluster;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+          asm volatile("mbarrier.arrive.release.cluster.shared::cta.b64 _, [%0];" ::"r"(pt::smem_u32(&stats_bar[par])) : "memory");
+          asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(map_to_peer(&stats_bar[par], rank ^ 1u)) : "memory");
+        }
+        {
+          const uint32_t parity = (uint32_t)(it >> 1) & 1u, bar = pt::smem_u32(&stats_bar[par]);
+          uint32_t ok = 0, spins = 0;
+          while (!ok) {
+            asm volatile("{\n\t.reg .pred P;\n\t"
+                         "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+                         "selp.u32 %0, 1, 0, P;\n\t}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+            if (!ok && ++spins > PT_SPIN_LIMIT) __trap();
+          }
+        }
+        float tn = 0.f, mean = 0.f, m2t = 0.f;
+#pragma unroll
+        for (int sidx = 0; sidx < 4; ++sidx) {             // fixed order: all four owners of a row get identical statistics
+          const float2 st = stats_s[par][sidx][row];
+          if (sidx == 0) { tn = 128.f; mean = st.x; m2t = st.y; }
+          else welford_merge(tn, mean, m2t, 128.f, st.x, st.y);
+        }
+        const float rstd = rsqrtf(m2t * (1.f / 512.f) + 1e-5f);
+        const int cls = p.labels ? __ldg(p.labels + min(m, p.M - 1) / p.label_rows) : 0;
+        const float* na = p.norm_a + (size_t)cls * 512;
+        const float* nb = p.norm_b + (size_t)cls * 512;
+        // ---- pass 2: normalise, affine (+ SiLU), store
+#pragma unroll 1
+        for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
+          const int n = n0 + c0;
+          uint32_t v[32];
+          pt::tmem_ld32(t_row + c0, v);
+          pt::tmem_ld_wait();
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n) + i);
+            f[4 * i] = __uint_as_float(v[4 * i]) + bb.x; f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + bb.y;
+            f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + bb.z; f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bb.w;
+          }
+          if (p.residual) add_residual_bf16(f, n);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 ga = __ldg(reinterpret_cast<const float4*>(na + n) + i);
+            const float4 gb = __ldg(reinterpret_cast<const float4*>(nb + n) + i);
+            f[4 * i] = (f[4 * i] - mean) * rstd * ga.x + gb.x;
+            f[4 * i + 1] = (f[4 * i + 1] - mean) * rstd * ga.y + gb.y;
+            f[4 * i + 2] = (f[4 * i + 2] - mean) * rstd * ga.z + gb.z;
+            f[4 * i + 3] = (f[4 * i + 3] - mean) * rstd * ga.w + gb.w;
+          }
+          if (p.row_norm == 1) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = f[i] / (1.f + __expf(-f[i]));
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(tile + lane * kTilePitch + i * 16) = make_uint4(
+                pt::pack_bf16x2(f[8 * i], f[8 * i + 1]), pt::pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                pt::pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pt::pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int rr = pr + 8 * j;
+            const long long ro = row_out[rr];
+            if (ro >= 0)
+              *(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + n) + pc) =
+                  *reinterpret_cast<const uint4*>(tile + rr * kTilePitch + pc * 16);
+          }
+        }
+        pt::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) pt::mbar_arrive(&tmem_empty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
 #pragma unroll 1
       for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
         const int n = n0 + c0;
@@ -322,6 +496,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
   pt::tc_fence_before();
   __syncthreads();
+  if constexpr (kRowNorm) cluster_sync_all();          // no CTA exits while its peer may still write into its smem
   if (warp == 2) pt::tmem_dealloc(tmem_base, C::kTmemCols);
 }
 
@@ -363,13 +538,35 @@ template <int BN>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
+    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
     attr_done = true;
   }
   const int tiles = ka.m_tiles * ka.N_tiles;
   const int grid = tiles < sms ? tiles : sms;
-  gemm_kernel<BN><<<grid, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, ka);
+  gemm_kernel<BN, false><<<grid, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, ka);
   PT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// row-norm variant: clusters of two CTAs, one 128-row tile per cluster step
+int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmem));
+    attr_done = true;
+  }
+  int clusters = sms / 2;
+  if (ka.m_tiles < clusters) clusters = ka.m_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = Cfg<256>::kSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true>, ta, tb, ka));
   return 0;
 }
 
@@ -411,7 +608,17 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   // A viewed as [a_rows / s, s * C] (tap j of a stride-2 conv = row j/2, column half j%2)
   if (d->a_rows % d->s) return pt::fail("pt_gemm_bf16: a_rows (%lld) not divisible by stride", d->a_rows);
   if (make_tmap(&ta, d->a, d->a_rows / d->s, (long long)d->s * d->C, (long long)d->s * d->a_pitch, BM)) return 1;
-  const int BN = (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
+  if (d->row_norm) {
+    if (d->row_norm < 1 || d->row_norm > 2) return pt::fail("pt_gemm_bf16: bad row_norm %d", d->row_norm);
+    if (d->N != 512 || d->n_valid != 512 || d->ocs != 1 || d->out_f32 || (d->residual && d->res_f32) || d->act != PT_ACT_NONE)
+      return pt::fail("pt_gemm_bf16: row_norm needs N = 512, bf16 row-major output, bf16 residual (or none), no activation");
+    if (!d->bias || !d->norm_a || !d->norm_b) return pt::fail("pt_gemm_bf16: row_norm needs bias, norm_a, norm_b");
+    if (d->labels && d->label_rows <= 0) return pt::fail("pt_gemm_bf16: label_rows must be positive");
+    if ((reinterpret_cast<uintptr_t>(d->norm_a) | reinterpret_cast<uintptr_t>(d->norm_b)) & 15)
+      return pt::fail("pt_gemm_bf16: norm tables must be 16-byte aligned");
+  }
+  const int BN = d->row_norm ? 256
+               : (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
   if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, BN)) return 1;
 
   GemmKernelArgs ka;
@@ -421,6 +628,8 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   ka.oss = d->oss; ka.ors = d->ors; ka.ocs = d->ocs; ka.rss = d->rss; ka.rrs = d->rrs;
   ka.out = d->out; ka.bias = d->bias; ka.residual = d->residual; ka.out_f32 = d->out_f32; ka.res_f32 = d->res_f32;
   ka.act = d->act; ka.slope = d->slope; ka.m_tiles = (d->M + BM - 1) / BM;
+  ka.row_norm = d->row_norm; ka.norm_a = d->norm_a; ka.norm_b = d->norm_b; ka.labels = d->labels; ka.label_rows = d->label_rows;
   cudaStream_t st = (cudaStream_t)stream;
+  if (d->row_norm) return launch_rownorm(ta, tb, ka, sms, st);
   return BN == 256 ? launch<256>(ta, tb, ka, sms, st) : launch<128>(ta, tb, ka, sms, st);
 }

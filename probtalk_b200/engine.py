@@ -168,7 +168,7 @@ class Plan:
     # -- GEMM recorders
     def gemm(self, a_t, a_rows, a_pitch, w: Weight, out_t, *, M, C_, s=1, base_row=0, rows_per_sample, t_valid,
              oss, ors, ocs=1, out_off=0, act=ACT_NONE, slope=0.2, residual=None, rss=0, rrs=0, res_off=0, a_off=0,
-             n_valid=None, use_bias=True):
+             n_valid=None, use_bias=True, row_norm=0, norm_a=None, norm_b=None, labels=None, label_rows=1):
         d = GemmDesc()
         d.a = a_t.data_ptr() + 2 * a_off
         d.a_rows, d.a_pitch = a_rows, a_pitch
@@ -188,7 +188,11 @@ class Plan:
             d.residual, d.res_f32 = None, 0
         d.rss, d.rrs = rss, rrs
         d.act, d.slope = act, slope
-        self.keep += [a_t, w, out_t, residual, d]
+        d.row_norm, d.label_rows = row_norm, label_rows
+        d.norm_a = norm_a.data_ptr() if norm_a is not None else None
+        d.norm_b = norm_b.data_ptr() if norm_b is not None else None
+        d.labels = labels.data_ptr() if labels is not None else None
+        self.keep += [a_t, w, out_t, residual, d, norm_a, norm_b, labels]
         # algorithmic FLOPs: real output rows x real output channels x real input channels (no padding / halo credit)
         flops = 2.0 * M * (t_valid / float(rows_per_sample)) * d.n_valid * w.taps * w.cin
         self.call(_lib.lib().pt_gemm_bf16, C.byref(d), flops=flops)
@@ -226,12 +230,12 @@ class Plan:
                       out_off=(out.H + ph) * out.C, act=act, slope=slope)
 
     def linear(self, a_t, M, w: Weight, out_t, *, out_cols=None, act=ACT_NONE, residual=None, rss=0, rrs=0,
-               rows_per_sample=None, out_off=0, a_pitch=None, a_off=0):
+               rows_per_sample=None, out_off=0, a_pitch=None, a_off=0, **norm):
         """Plain row-major GEMM: out[m, :] = act(a[m, :] @ W^T + b (+ residual))."""
         ors = out_cols if out_cols is not None else w.n_valid
         rps = rows_per_sample or max(M, 1)
         self.gemm(a_t, M, a_pitch or w.Cp, w, out_t, M=M, C_=w.Cp, rows_per_sample=rps, t_valid=rps,
-                  oss=rps * ors, ors=ors, out_off=out_off, act=act, residual=residual, rss=rss, rrs=rrs, a_off=a_off)
+                  oss=rps * ors, ors=ors, out_off=out_off, act=act, residual=residual, rss=rss, rrs=rrs, a_off=a_off, **norm)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -392,6 +396,10 @@ class StyleWeights:
         # emb_layers_2 = Linear(SiLU(class_embed[label])) depends on the label only: tabulate it per class (fp32)
         self.mod = torch.nn.functional.linear(torch.nn.functional.silu(class_embed), w, b).contiguous()   # [n_classes, 1024]
         self.out = prep_linear(sd[p + ".out_layers_2.2.weight"], sd[p + ".out_layers_2.2.bias"], device)
+        # fused epilogue form:  LN(h)*(1+scale)+shift = (h-mean)*rstd * A[c] + B[c]
+        scale, shift = self.mod[:, :D_MODEL], self.mod[:, D_MODEL:]
+        self.norm_a = (self.gamma[None] * (1 + scale)).contiguous()
+        self.norm_b = (self.beta[None] * (1 + scale) + shift).contiguous()
 
 
 class LayerWeights:
@@ -427,8 +435,9 @@ class StackPlanner:
            accumulate across layers); r: pre-norm sum x + style(...) in bf16; LayerNorm statistics are fp32
     memb : bf16 memory rows [B*Mem, 512]; labels int32 [B]."""
 
-    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device):
+    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device, fused=True):
         self.p, self.W, self.B, self.N, self.Mem = plan, W, B, N, Mem
+        self.fused = fused
         M = B * N
         self.M = M
         z = lambda *s, dt=BF16: torch.zeros(*s, dtype=dt, device=device)
@@ -447,15 +456,23 @@ class StackPlanner:
     def record_memory_kv(self):
         self.p.linear(self.memb, self.B * self.Mem, self.W.kv_all, self.kv)
 
-    def _style_residual_norm(self, lw: LayerWeights, i):
-        """x = norm_i( x + style_i(proj) )   (PTransformer.py:329-331 with :134-140)."""
-        L = _lib.lib()
+    def _sublayer_tail(self, lw: LayerWeights, i, a_t, w_proj: Weight):
+        """x = norm_i( x + style_i( proj(a) ) )   (PTransformer.py:329-331 with :134-140, :344-364) as two fused GEMMs:
+             sil = SiLU( LN(a W_proj^T + b) (1+scale) + shift )         [row-norm epilogue, per-class tables]
+             x   = LN_i( sil W_style^T + b + x )                         [row-norm epilogue, residual in place]"""
         st = lw.styles[i]
         p, M = self.p, self.M
+        g, b = lw.norms[i]
+        if self.fused:
+            p.linear(a_t, M, w_proj, self.sil, row_norm=1, norm_a=st.norm_a, norm_b=st.norm_b, labels=self.labels,
+                     label_rows=self.N)
+            p.linear(self.sil, M, st.out, self.xb, residual=self.xb, rss=0, rrs=D_MODEL, row_norm=2, norm_a=g, norm_b=b)
+            return
+        L = _lib.lib()
+        p.linear(a_t, M, w_proj, self.proj)
         p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
                self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
         p.linear(self.sil, M, st.out, self.r)
-        g, b = lw.norms[i]
         # the residual add rides in the LayerNorm pass (a row-local read) instead of the GEMM epilogue
         p.call(L.pt_layernorm512, self.r.data_ptr(), 0, self.xb.data_ptr(), g.data_ptr(), b.data_ptr(), None,
                self.xb.data_ptr(), M)
@@ -471,20 +488,17 @@ class StackPlanner:
             p.call(L.pt_attention, self.qkv.data_ptr(), 3 * D_MODEL, self.qkv.data_ptr() + 2 * D_MODEL, 3 * D_MODEL,
                    self.qkv.data_ptr() + 4 * D_MODEL, 3 * D_MODEL, self.att.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM,
                    N, N, scale)
-            p.linear(self.att, M, lw.sa_out, self.proj)
-            self._style_residual_norm(lw, 0)
+            self._sublayer_tail(lw, 0, self.att, lw.sa_out)
             # cross attention over the memory
             p.linear(self.xb, M, lw.ca_q, self.q)
             kv_stride = 2 * D_MODEL * nl
             kptr = self.kv.data_ptr() + 2 * (l * 2 * D_MODEL)
             p.call(L.pt_attention, self.q.data_ptr(), D_MODEL, kptr, kv_stride, kptr + 2 * D_MODEL, kv_stride,
                    self.att.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM, N, Mem, scale)
-            p.linear(self.att, M, lw.ca_out, self.proj)
-            self._style_residual_norm(lw, 1)
+            self._sublayer_tail(lw, 1, self.att, lw.ca_out)
             # feed forward
             p.linear(self.xb, M, lw.ff1, self.ff, act=ACT_RELU)
-            p.linear(self.ff, M, lw.ff2, self.proj)
-            self._style_residual_norm(lw, 2)
+            self._sublayer_tail(lw, 2, self.ff, lw.ff2)
 
 
 # ----------------------------------------------------------------------------------------------

@@ -86,7 +86,8 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
          base_row: int = 0, rows_per_sample: int = None, t_valid: int = None, n_valid: int = None,
          oss: int = 0, ors: int = None, ocs: int = 1, out_offset: int = 0, bias: torch.Tensor = None,
          residual: torch.Tensor = None, rss: int = 0, rrs: int = 0, res_offset: int = 0, act: int = ACT_NONE,
-         slope: float = 0.2, a_rows: int = None, a_pitch: int = None, a_offset: int = 0):
+         slope: float = 0.2, a_rows: int = None, a_pitch: int = None, a_offset: int = 0, row_norm: int = 0,
+         norm_a: torch.Tensor = None, norm_b: torch.Tensor = None, labels: torch.Tensor = None, label_rows: int = 1):
     """Launch the tensor-core contraction engine (see pt_gemm_bf16 in include/probtalk_b200.h).
     ``a`` / ``out`` / ``residual`` are flat device buffers; offsets are in elements."""
     _need_cuda(a, w, out, bias, residual)
@@ -119,5 +120,6 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
         d.res_f32 = 0
     d.rss, d.rrs = rss, rrs
     d.act, d.slope = act, slope
+    d.row_norm, d.norm_a, d.norm_b, d.labels, d.label_rows = row_norm, _ptr(norm_a), _ptr(norm_b), _ptr(labels), label_rows
     check(_lib.lib().pt_gemm_bf16(C.byref(d), _stream()), "pt_gemm_bf16")
     return out

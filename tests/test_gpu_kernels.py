@@ -189,3 +189,34 @@ def test_pack_and_blend_match_torch():
     out = torch.zeros(B, Cc, T, device="cuda")
     _lib.check(L.pt_interp_blend(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), Tpred, out.data_ptr(), B, Cc, T, 2, _st()))
     assert (out - (src * mask * mask + interp * (1 - mask))).abs().max() < 1e-5
+
+
+@pytest.mark.parametrize("M,K", [(1000, 512), (128, 2048), (90112 // 8, 512)])
+@pytest.mark.parametrize("mode", [1, 2])
+def test_gemm_rownorm_cluster_epilogue(M, K, mode):
+    """Fused LayerNorm epilogue (2-CTA cluster exchanging row statistics through DSMEM) vs torch."""
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M + K + mode)
+    N = 512
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    v = a.float() @ w.float().t() + bias
+    if mode == 1:
+        rows = 8
+        na = torch.rand(4, N, device="cuda", generator=g) + 0.5
+        nb = torch.randn(4, N, device="cuda", generator=g)
+        labels = (torch.arange((M + rows - 1) // rows, device="cuda") % 4).int()
+        out = torch.zeros(M, N, device="cuda", dtype=torch.bfloat16)
+        ops.gemm(a, w, out, M=M, C_=K, bias=bias, ors=N, row_norm=1, norm_a=na, norm_b=nb, labels=labels, label_rows=rows)
+        cls = labels.long().repeat_interleave(rows)[:M]
+        y = F.layer_norm(v, (N,), None, None, 1e-5) * na[cls] + nb[cls]
+        ref = F.silu(y)
+    else:
+        na = torch.rand(1, N, device="cuda", generator=g) + 0.5
+        nb = torch.randn(1, N, device="cuda", generator=g)
+        x = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+        out = x.clone()                                   # residual aliases the output (x = LN(x + s))
+        ops.gemm(a, w, out, M=M, C_=K, bias=bias, ors=N, residual=out, rrs=N, row_norm=2, norm_a=na, norm_b=nb)
+        ref = F.layer_norm(v + x.float(), (N,), na[0], nb[0], 1e-5)
+    assert (out.float() - ref).abs().max() < 0.06
