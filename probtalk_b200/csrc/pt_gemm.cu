@@ -18,6 +18,7 @@
 //   warps 4-11 epilogue : tcgen05.ld (lane = output row), bias / residual / activation, smem-staged 64-byte row stores
 // so the epilogue of tile i overlaps the main loop of tile i+1.
 #include <cuda.h>
+#include <stdlib.h>
 #include "pt_common.cuh"
 #include "pt_host.h"
 #include "pt_gemm.h"
@@ -97,7 +98,10 @@ __device__ __forceinline__ void welford_merge(float& n, float& mean, float& m2, 
 // kRowNorm: launched as clusters of two CTAs; CTA `rank` owns columns [rank*256, rank*256+256) of the same 128
 // rows, and the two exchange per-row (mean, M2) partials through distributed shared memory so that the epilogue can
 // apply a LayerNorm over the full 512-wide row (StylizationBlock_V3 / norm1-3 of the reference) in place.
-template <int BN, bool kRowNorm>
+// kCL > 1 (plain variant only): clusters of kCL CTAs along M work on kCL consecutive 128-row tiles of the SAME
+// column tile; every CTA loads 1/kCL of the weight box and multicasts it to the whole cluster, so weight traffic
+// from L2 drops by kCL (these GEMMs have K = 512..2048 and are L2-bandwidth bound with private weight loads).
+template <int BN, bool kRowNorm, int kCL>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const GemmKernelArgs p) {
@@ -118,19 +122,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __shared__ uint64_t stats_bar[2];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = kRowNorm ? cluster_ctarank() : 0u;
-  const int tile_first = kRowNorm ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int tile_stride = kRowNorm ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  const int n_tiles_total = kRowNorm ? p.m_tiles : p.m_tiles * p.N_tiles;
-  auto tile_m0 = [&](int tile) { return kRowNorm ? tile * BM : (tile / p.N_tiles) * BM; };
+  static_assert(!(kRowNorm && kCL != 1), "row-norm clusters are along N");
+  constexpr int kClusterSize = kRowNorm ? 2 : kCL;
+  const uint32_t rank = (kClusterSize > 1) ? cluster_ctarank() : 0u;
+  const int tile_first = (int)(blockIdx.x / kClusterSize);
+  const int tile_stride = (int)(gridDim.x / kClusterSize);
+  // kRowNorm: one "tile" = a 128-row block (the two CTAs split its 512 columns);
+  // kCL > 1 : one "tile" = kCL consecutive 128-row blocks x one column tile (CTA `rank` owns block rank)
+  const int m_super = (p.m_tiles + kCL - 1) / kCL;
+  const int n_tiles_total = kRowNorm ? p.m_tiles : m_super * p.N_tiles;
+  auto tile_m0 = [&](int tile) { return kRowNorm ? tile * BM : ((tile / p.N_tiles) * kCL + (int)rank) * BM; };
   auto tile_n0 = [&](int tile) { return kRowNorm ? (int)rank * BN : (tile % p.N_tiles) * BN; };
+  constexpr uint16_t kMcMask = (uint16_t)((1u << kCL) - 1u);
 
   if (warp == 0 && lane == 0) {
     pt::tma_prefetch_desc(&tmap_a);
     pt::tma_prefetch_desc(&tmap_b);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], kCL); }
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], kEpiWarps); }
     if constexpr (kRowNorm) { pt::mbar_init(&stats_bar[0], 2 * kEpiWarps); pt::mbar_init(&stats_bar[1], 2 * kEpiWarps); }
     pt::fence_mbar_init();
@@ -142,7 +152,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   pt::tc_fence_before();
   __syncthreads();
   pt::tc_fence_after();
-  if constexpr (kRowNorm) cluster_sync_all();          // the peer's barriers exist before anyone arrives on them
+  if constexpr (kClusterSize > 1) cluster_sync_all();  // the peers' barriers exist before anyone arrives on them
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -157,7 +167,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
           pt::mbar_expect_tx(&full[stage], C::kStageBytes);
           pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
-          pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
+          if constexpr (kCL == 1) {
+            pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
+          } else {
+            // this CTA's slice of the weight box (BN / kCL rows), delivered to every CTA of the cluster
+            constexpr int kSliceRows = BN / kCL;
+            pt::tma_load_2d_mc(sa + C::kABytes + rank * (kSliceRows * 128), &tmap_b, &full[stage], kk * BK,
+                               n0 + (int)rank * kSliceRows, kMcMask);
+          }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -182,7 +199,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
                           (kk | k) ? 1u : 0u);
           }
-          pt::umma_commit(&empty[stage]);                 // slot reusable once these MMAs have read it
+          if constexpr (kCL == 1) pt::umma_commit(&empty[stage]);   // slot reusable once these MMAs have read it
+          else pt::umma_commit_mc(&empty[stage], kMcMask);          // ... in every CTA that multicasts into it
           if (kk == p.K_iters - 1) pt::umma_commit(&tmem_full[acc]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
@@ -273,7 +291,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         stats_s[par][src][row] = make_float2(wmean, wm2);
         const uint32_t peer = map_to_peer(&stats_s[par][src][row], rank ^ 1u);
         asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(peer), "f"(wmean), "f"(wm2) : "memory");
-        asm volatile("fence.acq_rel.cluster;" ::: "memory");
+        // no cluster fence here: a fence at cluster scope costs MEMBAR.GPU + an L1 invalidate (CCTL.IVALL) per tile.
+        // __syncwarp orders the lanes' stores before lane 0's arrive.release.cluster, which is cumulative.
         __syncwarp();
         if (lane == 0) {
           asm volatile("mbarrier.arrive.release.cluster.shared::cta.b64 _, [%0];" ::"r"(pt::smem_u32(&stats_bar[par])) : "memory");
@@ -283,8 +302,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           const uint32_t parity = (uint32_t)(it >> 1) & 1u, bar = pt::smem_u32(&stats_bar[par]);
           uint32_t ok = 0, spins = 0;
           while (!ok) {
+            // the partials land in THIS CTA's shared memory (never cached in L1), so the default CTA-scope
+            // acquire suffices and avoids the per-poll CCTL.IVALL that a cluster-scope acquire emits
             asm volatile("{\n\t.reg .pred P;\n\t"
-                         "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+                         "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
                          "selp.u32 %0, 1, 0, P;\n\t}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
             if (!ok && ++spins > PT_SPIN_LIMIT) __trap();
           }
@@ -325,8 +346,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             f[4 * i + 3] = (f[4 * i + 3] - mean) * rstd * ga.w + gb.w;
           }
           if (p.row_norm == 1) {
+            // SiLU(x) = x * sigmoid(x) = 0.5 x (1 + tanh(x / 2)): one MUFU op per element
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = f[i] / (1.f + __expf(-f[i]));
+            for (int i = 0; i < 32; ++i) {
+              float th;
+              asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(0.5f * f[i]));
+              f[i] = 0.5f * f[i] * (1.f + th);
+            }
           }
           __syncwarp();
 #pragma unroll
@@ -496,7 +522,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
   pt::tc_fence_before();
   __syncthreads();
-  if constexpr (kRowNorm) cluster_sync_all();          // no CTA exits while its peer may still write into its smem
+  if constexpr (kClusterSize > 1) cluster_sync_all();  // no CTA exits while a peer may still write into its smem
   if (warp == 2) pt::tmem_dealloc(tmem_base, C::kTmemCols);
 }
 
@@ -534,17 +560,32 @@ int make_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols,
   return 0;
 }
 
-template <int BN>
+template <int BN, int CL>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
+    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, false, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
     attr_done = true;
   }
-  const int tiles = ka.m_tiles * ka.N_tiles;
-  const int grid = tiles < sms ? tiles : sms;
-  gemm_kernel<BN, false><<<grid, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, ka);
-  PT_CUDA(cudaGetLastError());
+  const int m_super = (ka.m_tiles + CL - 1) / CL;
+  const int tiles = m_super * ka.N_tiles;
+  int clusters = sms / CL;
+  if (tiles < clusters) clusters = tiles;
+  if constexpr (CL == 1) {
+    gemm_kernel<BN, false, 1><<<clusters, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, ka);
+    PT_CUDA(cudaGetLastError());
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CL * clusters);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = Cfg<BN>::kSmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, ka));
+  }
   return 0;
 }
 
@@ -552,7 +593,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& k
 int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmem));
+    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmem));
     attr_done = true;
   }
   int clusters = sms / 2;
@@ -566,7 +607,7 @@ int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKerne
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true>, ta, tb, ka));
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true, 1>, ta, tb, ka));
   return 0;
 }
 
@@ -619,7 +660,18 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   }
   const int BN = d->row_norm ? 256
                : (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
-  if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, BN)) return 1;
+  // weight multicast across clusters of CTAs along M pays off once there are enough row tiles to fill the chip
+  const long long m_tiles_ll = (d->M + BM - 1) / BM;
+  int CL = 1;
+  if (!d->row_norm && BN == 256) {
+    if (m_tiles_ll * (d->N / BN) >= 4LL * sms) CL = 4;
+    else if (m_tiles_ll * (d->N / BN) >= 2LL * sms) CL = 2;
+  }
+  {
+    const char* e = getenv("PT_GEMM_CLUSTER");            // developer override (1, 2 or 4)
+    if (e && !d->row_norm && BN == 256) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) CL = v; }
+  }
+  if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, BN / CL)) return 1;
 
   GemmKernelArgs ka;
   ka.M = d->M; ka.N_tiles = d->N / BN; ka.c_iters = d->C / BK; ka.K_iters = d->taps * ka.c_iters;
@@ -631,5 +683,8 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   ka.row_norm = d->row_norm; ka.norm_a = d->norm_a; ka.norm_b = d->norm_b; ka.labels = d->labels; ka.label_rows = d->label_rows;
   cudaStream_t st = (cudaStream_t)stream;
   if (d->row_norm) return launch_rownorm(ta, tb, ka, sms, st);
-  return BN == 256 ? launch<256>(ta, tb, ka, sms, st) : launch<128>(ta, tb, ka, sms, st);
+  if (BN == 128) return launch<128, 1>(ta, tb, ka, sms, st);
+  if (CL == 4) return launch<256, 4>(ta, tb, ka, sms, st);
+  if (CL == 2) return launch<256, 2>(ta, tb, ka, sms, st);
+  return launch<256, 1>(ta, tb, ka, sms, st);
 }

@@ -435,9 +435,11 @@ class StackPlanner:
            accumulate across layers); r: pre-norm sum x + style(...) in bf16; LayerNorm statistics are fp32
     memb : bf16 memory rows [B*Mem, 512]; labels int32 [B]."""
 
-    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device, fused=True):
+    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device, fuse_style=True, fuse_norm=False):
         self.p, self.W, self.B, self.N, self.Mem = plan, W, B, N, Mem
-        self.fused = fused
+        # fuse_style: out-proj / FF2 GEMM + style LayerNorm-modulation-SiLU in one kernel (cluster row-norm epilogue)
+        # fuse_norm : style GEMM + residual + LayerNorm in one kernel (correct, but slower than GEMM + LN pass today)
+        self.fuse_style, self.fuse_norm = fuse_style, fuse_norm
         M = B * N
         self.M = M
         z = lambda *s, dt=BF16: torch.zeros(*s, dtype=dt, device=device)
@@ -463,15 +465,17 @@ class StackPlanner:
         st = lw.styles[i]
         p, M = self.p, self.M
         g, b = lw.norms[i]
-        if self.fused:
+        L = _lib.lib()
+        if self.fuse_style:
             p.linear(a_t, M, w_proj, self.sil, row_norm=1, norm_a=st.norm_a, norm_b=st.norm_b, labels=self.labels,
                      label_rows=self.N)
+        else:
+            p.linear(a_t, M, w_proj, self.proj)
+            p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
+                   self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
+        if self.fuse_norm:
             p.linear(self.sil, M, st.out, self.xb, residual=self.xb, rss=0, rrs=D_MODEL, row_norm=2, norm_a=g, norm_b=b)
             return
-        L = _lib.lib()
-        p.linear(a_t, M, w_proj, self.proj)
-        p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
-               self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
         p.linear(self.sil, M, st.out, self.r)
         # the residual add rides in the LayerNorm pass (a row-local read) instead of the GEMM epilogue
         p.call(L.pt_layernorm512, self.r.data_ptr(), 0, self.xb.data_ptr(), g.data_ptr(), b.data_ptr(), None,
