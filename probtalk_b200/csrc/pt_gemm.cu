@@ -660,13 +660,10 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   }
   const int BN = d->row_norm ? 256
                : (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
-  // weight multicast across clusters of CTAs along M pays off once there are enough row tiles to fill the chip
-  const long long m_tiles_ll = (d->M + BM - 1) / BM;
+  // Weight multicast across clusters of CTAs along M (CL = 2 / 4) is implemented and tested, but measured no
+  // faster than private loads on B200 (CL = 2: +2 %, CL = 4: -40 %, profiles/r01_notes.md): these GEMMs are bound by
+  // the bytes in flight per SM, not by L2 bandwidth.  Default off.
   int CL = 1;
-  if (!d->row_norm && BN == 256) {
-    if (m_tiles_ll * (d->N / BN) >= 4LL * sms) CL = 4;
-    else if (m_tiles_ll * (d->N / BN) >= 2LL * sms) CL = 2;
-  }
   {
     const char* e = getenv("PT_GEMM_CLUSTER");            // developer override (1, 2 or 4)
     if (e && !d->row_norm && BN == 256) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) CL = v; }
