@@ -10,6 +10,12 @@
 #include "pt_common.cuh"
 #include "pt_host.h"
 #include "../../include/probtalk_b200.h"
+#include <stdlib.h>
+
+// tcgen05 implementation for up to 256 keys (pt_attn_tc.cu)
+int pt_attention_tc(const void* q, long long q_stride, const void* k, long long k_stride, const void* v,
+                    long long v_stride, void* out, long long out_stride, int B, int heads, int Nq, int Nk, float scale,
+                    cudaStream_t st);
 
 namespace {
 
@@ -228,6 +234,14 @@ extern "C" int pt_attention(const void* q, long long q_stride, const void* k, lo
   if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15)
     return pt::fail("pt_attention: q/k/v must be 16-byte aligned");
   if ((out_stride & 1) || (reinterpret_cast<uintptr_t>(out) & 3)) return pt::fail("pt_attention: out must be 4-byte aligned");
+  {
+    // tensor-core (tcgen05) path for the sequence lengths of this model; the mma.sync kernel below covers
+    // longer key sequences (and PT_ATTN_LEGACY=1 forces it, for A/B measurements)
+    static const bool legacy = getenv("PT_ATTN_LEGACY") != nullptr;
+    if (Nk <= 256 && !legacy)
+      return pt_attention_tc(q, q_stride, k, k_stride, v, v_stride, out, out_stride, B, heads, Nq, Nk, scale,
+                             (cudaStream_t)stream);
+  }
   AttnArgs a;
   a.q = (const __nv_bfloat16*)q; a.k = (const __nv_bfloat16*)k; a.v = (const __nv_bfloat16*)v;
   a.out = (__nv_bfloat16*)out;
