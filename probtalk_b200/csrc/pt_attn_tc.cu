@@ -23,8 +23,16 @@ struct AttnTcArgs {
   long long out_stride;
   int heads, Nq, Nk, NKP;          // NKP = keys padded to 16
   int B, m_tiles;                  // m_tiles = ceil(Nq / 128)
+  int tmem_cols, o_col;            // TMEM allocation (power of two) and the column where O starts
+  int nstage;                      // Q/K/V smem stages (2 = prefetch the next unit)
   float scale_log2e;
 };
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 // smem matrix descriptor, MN-major operand, SWIZZLE_128B: 64 MN-elements (128 B) per row, rows = K index;
 // SBO = stride between groups of 8 K-rows (1024 B); LBO = stride between 64-element MN atoms (single atom here)
@@ -38,7 +46,7 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr) {
   return d;
 }
 
-__global__ void __launch_bounds__(kThreadsTc, 1)
+__global__ void __launch_bounds__(kThreadsTc, 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const AttnTcArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -47,7 +55,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const uint32_t kv_pad = (kv_bytes + 1023u) & ~1023u;
   const uint32_t stage_bytes = kQBytes + 2 * kv_pad;
   const int p_atoms = (a.NKP + 63) / 64;
-  uint8_t* p_smem = smem + 2 * stage_bytes;
+  uint8_t* p_smem = smem + (size_t)a.nstage * stage_bytes;
   __shared__ uint64_t bars[9];
   uint64_t* qkv_full = bars;        // [2]
   uint64_t* qkv_empty = bars + 2;   // [2]
@@ -68,20 +76,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     pt::mbar_init(o_full, 1); pt::mbar_init(o_free, 4);
     pt::fence_mbar_init();
   }
-  if (warp == 1) { pt::tmem_alloc(&tmem_slot, 512); pt::tmem_relinquish(); }
+  if (warp == 1) { pt::tmem_alloc(&tmem_slot, (uint32_t)a.tmem_cols); pt::tmem_relinquish(); }
   pt::tc_fence_before();
   __syncthreads();
   pt::tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  const uint32_t tmem_s = tmem, tmem_o = tmem + 256;
+  const uint32_t tmem_s = tmem, tmem_o = tmem + (uint32_t)a.o_col;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int it = 0;
       for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+        const int st = (a.nstage == 2) ? (it & 1) : 0;
+        const uint32_t ph = (uint32_t)((a.nstage == 2) ? (it >> 1) : it) & 1u;
         const int mt = u % a.m_tiles, bh = u / a.m_tiles;
         const int h = bh % a.heads, b = bh / a.heads;
         pt::mbar_wait(&qkv_empty[st], ph ^ 1);
@@ -99,8 +107,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const uint32_t idesc_o = pt::umma_idesc_bf16(kQRows, 64) | (1u << 16);       // B operand (V) is MN-major
       int it = 0;
       for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (uint32_t)(it >> 1) & 1u, up = (uint32_t)it & 1u;
+        const int st = (a.nstage == 2) ? (it & 1) : 0;
+        const uint32_t ph = (uint32_t)((a.nstage == 2) ? (it >> 1) : it) & 1u, up = (uint32_t)it & 1u;
         const uint32_t sq = pt::smem_u32(smem + (size_t)st * stage_bytes);
         const uint32_t sk = sq + kQBytes, sv = sk + kv_pad;
         pt::mbar_wait(&qkv_full[st], ph);
@@ -154,8 +162,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const float p0 = (c0 + 2 * i < a.Nk) ? exp2f(fmaf(__uint_as_float(v[2 * i]), a.scale_log2e, -mxs)) : 0.f;
-          const float p1 = (c0 + 2 * i + 1 < a.Nk) ? exp2f(fmaf(__uint_as_float(v[2 * i + 1]), a.scale_log2e, -mxs)) : 0.f;
+          const float p0 = (c0 + 2 * i < a.Nk) ? ex2(fmaf(__uint_as_float(v[2 * i]), a.scale_log2e, -mxs)) : 0.f;
+          const float p1 = (c0 + 2 * i + 1 < a.Nk) ? ex2(fmaf(__uint_as_float(v[2 * i + 1]), a.scale_log2e, -mxs)) : 0.f;
           sum += p0 + p1;
           pk[i] = pt::pack_bf16x2(p0, p1);
         }
@@ -203,7 +211,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   }
   pt::tc_fence_before();
   __syncthreads();
-  if (warp == 1) pt::tmem_dealloc(tmem, 512);
+  if (warp == 1) pt::tmem_dealloc(tmem, (uint32_t)a.tmem_cols);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -249,7 +257,22 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
   if (make_map(&tk, k, (long long)B * Nk, (long long)heads * 64, k_stride, a.NKP)) return 1;
   if (make_map(&tv, v, (long long)B * Nk, (long long)heads * 64, v_stride, a.NKP)) return 1;
   const uint32_t kv_pad = ((uint32_t)a.NKP * 128u + 1023u) & ~1023u;
-  const size_t smem = 1024 + 2 * (size_t)(kQBytes + 2 * kv_pad) + (size_t)((a.NKP + 63) / 64) * kAtomBytes;
+  const size_t stage = kQBytes + 2 * (size_t)kv_pad, ptile = (size_t)((a.NKP + 63) / 64) * kAtomBytes;
+  // TMEM: S (NKP columns) + O (64 columns), rounded to a power of two; smaller allocations let several CTAs share an SM
+  a.o_col = a.NKP;
+  a.tmem_cols = 32;
+  while (a.tmem_cols < a.NKP + 64) a.tmem_cols *= 2;
+  const int by_tmem = 512 / a.tmem_cols;
+  // the unit chain (MMA -> softmax -> MMA -> store) is latency bound, so co-resident CTAs matter more than prefetch depth
+  const size_t sm_smem = 227 * 1024;
+  int per_sm = 1;
+  a.nstage = 2;
+  for (int want = (by_tmem < 2 ? by_tmem : 2); want >= 1; --want) {
+    if ((1024 + 2 * stage + ptile + 1024) * want <= sm_smem) { per_sm = want; a.nstage = 2; break; }
+    if ((1024 + stage + ptile + 1024) * want <= sm_smem) { per_sm = want; a.nstage = 1; break; }
+  }
+  const size_t smem = 1024 + a.nstage * stage + ptile;
+  if (smem > sm_smem) return pt::fail("pt_attention: Nk=%d does not fit in shared memory", Nk);
   static size_t configured = 0;
   if (smem > configured) {
     PT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -259,7 +282,8 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int n_units = B * heads * a.m_tiles;
-  attention_tc_kernel<<<n_units < sms ? n_units : sms, kThreadsTc, smem, st>>>(tq, tk, tv, a);
+  const int grid_max = sms * per_sm;
+  attention_tc_kernel<<<n_units < grid_max ? n_units : grid_max, kThreadsTc, smem, st>>>(tq, tk, tv, a);
   PT_CUDA(cudaGetLastError());
   return 0;
 }
