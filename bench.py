@@ -177,8 +177,8 @@ def run_ours(args):
     B = args.batch
     vq, pst, rst = S.make_vq_state(0), S.make_predictor_state(1), S.make_refiner_state(5)
     VW, PW, RW = E.VQVAEWeights(vq, dev), E.PredictorWeights(pst, dev), E.RefinerWeights(rst, dev)
-    pred = E.PredictorPlan(PW, VW, B, T_FRAMES)
-    ref = E.RefinerPlan(RW, B, T_FRAMES, T_FRAMES)
+    pred = E.PredictorPlan(PW, VW, B, T_FRAMES, use_graph=not args.no_graph)
+    ref = E.RefinerPlan(RW, B, T_FRAMES, T_FRAMES, use_graph=not args.no_graph)
     aud, gt, mask, ids = synthetic_batch(B, 1004 + rank, dev)
     gather_buf = torch.empty(world * B, 376, T_FRAMES, device=dev) if (world > 1 and rank == 0) else None
     launches_per_step = pred.launches + ref.launches
@@ -235,6 +235,7 @@ def run_ours(args):
                 "config": {"workload": "config 4: s2g_body_predictor + s2g_body_refiner + PQ-VAE decode, one 180-frame window",
                            "clips_per_gpu": B, "global_clips": world * B, "frames": T_FRAMES, "maskgit_T": 8,
                            "parallelism": "dp%d (clips sharded, weights replicated, NCCL gather of poses)" % world,
+                           "launch": "eager" if args.no_graph else "one CUDA graph per model per window",
                            "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2; no flush needed"},
                 "clocks": clocks, "gpu_launches": launches_per_step * args.steps,
                 "roofline": {"bound": "tensor", "kernel": "gemm_kernel (tcgen05 bf16)", "achieved": ach, "peak": pk["tf_sust"],
@@ -337,6 +338,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1024, help="clips per GPU per step (BASELINE config 4 sweeps 64-1024)")
     ap.add_argument("--ref-batch", type=int, default=16, help="clips per CPU-reference step (bounded sample)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

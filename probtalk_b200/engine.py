@@ -570,7 +570,7 @@ class PredictorPlan:
     """One (B, T) bucket of s2g_body_predictor inference on already-batched inputs:
          aud [B,768,T], gt_poses [B,376,T], mask [B,1,T], labels [B]  ->  poses [B,376,T], codes [B,T',G]."""
 
-    def __init__(self, PW: PredictorWeights, VW: VQVAEWeights, B, T, maskgit_T=8):
+    def __init__(self, PW: PredictorWeights, VW: VQVAEWeights, B, T, maskgit_T=8, use_graph=True):
         dev = PW.device
         self.PW, self.VW, self.B, self.T, self.steps_T = PW, VW, B, T, maskgit_T
         L = _lib.lib()
@@ -668,6 +668,7 @@ class PredictorPlan:
         self.dec.plan.call(L.pt_interp_blend, self.gt.data_ptr(), self.mask.data_ptr(), self.dec.out.data_ptr(), self.dec.T_out,
                            self.out.data_ptr(), B, PW.mot_dim, T, 2)
         self.launches = pa.launches + maskgit_T * (pb.launches + 1) + self.dec.plan.launches
+        self.use_graph, self.graph, self._warm = use_graph, None, False
 
     def plans_in_order(self):
         seq = [self.plan_cond]
@@ -701,10 +702,30 @@ class PredictorPlan:
             self.u.copy_(noise[0]); self.gumbel.copy_(noise[1])
         else:
             self.draw_noise(generator)
+        self._replay()
+        return self.out, self.codes
+
+    def _launch_all(self):
         self.cur.fill_(MASK_ID)
         for pl in self.plans_in_order():
             pl.run()
-        return self.out, self.codes
+
+    def _replay(self):
+        """First call launches eagerly (also the warm-up that sets kernel attributes); from the second call on the
+        whole window (~750 launches) is replayed as ONE CUDA graph, which removes the host launch cost that
+        dominates small batches."""
+        if not self.use_graph:
+            return self._launch_all()
+        if self.graph is None:
+            if not self._warm:
+                self._warm = True
+                return self._launch_all()
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._launch_all()
+            self.graph = g
+        self.graph.replay()
 
 
 # ----------------------------------------------------------------------------------------------
@@ -731,7 +752,7 @@ class RefinerWeights:
 class RefinerPlan:
     """One (B, T) bucket: aud [B,768,T], gt [B,376,T], mask [B,1,T], pred [B,376,Tpred], labels [B] -> [B,376,T]."""
 
-    def __init__(self, RW: RefinerWeights, B, T, T_pred=None):
+    def __init__(self, RW: RefinerWeights, B, T, T_pred=None, use_graph=True):
         dev = RW.device
         self.RW, self.B, self.T = RW, B, T
         self.T_pred = T_pred or T
@@ -768,9 +789,22 @@ class RefinerPlan:
         p.call(L.pt_interp_blend, self.gt.data_ptr(), self.mask.data_ptr(), self.raw.data_ptr(), T, self.out.data_ptr(), B,
                RW.in_dim, T, 1)
         self.launches = p.launches
+        self.use_graph, self.graph, self._warm = use_graph, None, False
         p.keep += [xin, xc]
 
     def run(self, aud, gt, mask, pred, labels):
         self.aud.copy_(aud); self.gt.copy_(gt); self.mask.copy_(mask); self.pred.copy_(pred); self.labels.copy_(labels)
-        self.plan.run()
+        if not self.use_graph:
+            self.plan.run()
+        elif self.graph is None and not self._warm:
+            self._warm = True
+            self.plan.run()
+        else:
+            if self.graph is None:
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self.plan.run()
+                self.graph = g
+            self.graph.replay()
         return self.out
