@@ -208,9 +208,7 @@ int launch_attn(const AttnArgs& a, int B, cudaStream_t st) {
     PT_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = pt::sm_count();
   int per_sm = (int)((227 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);   // __launch_bounds__(192, 2)
   const int n_pairs = B * a.heads;

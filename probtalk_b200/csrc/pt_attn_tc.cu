@@ -278,9 +278,7 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
     PT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = pt::sm_count();
   const int n_units = B * heads * a.m_tiles;
   const int grid_max = sms * per_sm;
   attention_tc_kernel<<<n_units < grid_max ? n_units : grid_max, kThreadsTc, smem, st>>>(tq, tk, tv, a);

@@ -641,9 +641,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   } else if (d->residual) {
     return pt::fail("pt_gemm_bf16: a residual needs a row-major output");
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = pt::sm_count();
 
   CUtensorMap ta, tb;
   // A viewed as [a_rows / s, s * C] (tap j of a stride-2 conv = row j/2, column half j%2)

@@ -18,6 +18,20 @@ inline int fail(const char* fmt, ...) {
   return 1;
 }
 
+// SM count of the current device, cached (cudaDeviceGetAttribute costs microseconds per call)
+inline int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int& c = cached[dev & 63];
+  if (c == 0) {
+    int v = 148;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    c = v;
+  }
+  return c;
+}
+
 }  // namespace pt
 
 #define PT_CUDA(expr)                                                                              \

@@ -3,20 +3,21 @@
 // Replaces ProductQuantization.get_code_indices + the per-group loop of .forward (eval) and
 // .quantize_all of the reference (nets/spg/vqvae_modules.py:546-555, :470-491, :557-569).
 //
-// Search = dense contraction:  score[r, j] = |c_j|^2 - 2 * x_r . c_j   (|x_r|^2 is constant per row
-// and cannot change the argmin).  One CTA owns up to 128 query rows of ONE sub-codebook:
-//   1. all 8 warps stage the rows and the 128x128 codebook into shared memory as split-bf16
-//      operands (x = x_hi + x_lo, c = c_hi + c_lo), K-major, SWIZZLE_128B;
-//   2. one thread issues 24 tcgen05.mma (hi*hi + hi*lo + lo*hi) into a 128x128 fp32 TMEM tile;
-//      dropped terms are O(2^-16), so the TMEM scores are within
-//      E = 2.5e-4 * |x| * max|c| (+ fp32 rounding) of the exact ones (checked on hardware by
-//      tests/test_pq_search.py through the score dump);
-//   3. the TMEM tile is scanned (lane = row, tcgen05.ld) for the smallest and second smallest score;
-//   4. rows whose top-2 gap is inside the error band are re-scored in fp32 with the reference's own
-//      formula  (sum x^2 + sum c^2) - 2 * dot,  FMA accumulation, lowest index winning ties -- so the
-//      emitted index is the fp32 answer for every row, and differs from the reference's only where
-//      the reference's own summation order decides (true gap below a few ulp of |x|^2).
-//
+// Search = dense contraction:  score[r, j] = |c_j|^2 - 2 * x_r . c_j   (|x_r|^2 is constant per row and
+// cannot change the argmin).  Persistent, warp-specialised CTAs; a CTA is bound to ONE sub-codebook and
+// walks 128-row query tiles of it:
+//   prologue      8 warps stage the 128x128 codebook once as split-bf16 operands (c = c_hi + c_lo), K-major,
+//                 SWIZZLE_128B, and its squared norms;
+//   loader warps  (4) stream the next tile's raw fp32 rows into smem with cp.async while the previous tile is in
+//                 the tensor core / being scanned, then split them (x = x_hi + x_lo) into the bf16 operand tile;
+//   MMA warp      one thread issues 24 tcgen05.mma per tile (hi*hi + hi*lo + lo*hi) into one of two 128-column
+//                 TMEM accumulators; dropped terms are O(2^-16), so scores are within
+//                 E = 2.5e-4 * |x| * max|c| of exact (checked on hardware by tests/test_gpu_pq.py);
+//   scan warps    (4) read the TMEM tile (lane = row) for the smallest and second smallest score; rows whose
+//                 top-2 gap is inside the error band are re-scored in fp32 with the reference's own formula
+//                 (sum x^2 + sum c^2) - 2 * dot, FMA accumulation, lowest index winning ties -- so the emitted
+//                 index is the fp32 answer for every row, and differs from the reference's only where the
+//                 reference's own summation order decides (true gap below a few ulp of |x|^2).
 // HBM traffic: z once (fp32), codebook from L2, int64 indices out.  No scratch memory.
 #include "pt_common.cuh"
 #include "pt_host.h"
@@ -26,27 +27,21 @@ namespace {
 constexpr int kD = 128;          // sub-vector width
 constexpr int kK = 128;          // codes per sub-codebook
 constexpr int kTileRows = 128;   // UMMA M
-constexpr int kThreads = 256;
+constexpr int kLoadWarps = 4, kScanWarps = 4;
+constexpr int kThreads = (kLoadWarps + 1 + kScanWarps) * 32;   // 288: loaders, MMA issuer, scanners
 constexpr uint32_t kOpBytes = kTileRows * kD * 2;   // one bf16 operand tile: 32 KB (two 64-col swizzle atoms)
 constexpr uint32_t kAtomBytes = kTileRows * 128;    // 16 KB
 constexpr float kBand = 2.5e-4f;                    // rigorous bound is ~9.3e-5 * |x||c| on the dot, x2 for the score
 
 struct PqSmem {
-  // operands (each 1024-B aligned): A_hi, A_lo, B_hi, B_lo
-  uint8_t ops[4][kOpBytes];
-  float sc2[kK];           // |c_j|^2 (fp32, deterministic order)
-  float sx2[kTileRows];    // |x_r|^2 (only used for the error band)
-  float pmin[2][kTileRows];
-  float pmin2[2][kTileRows];
-  int pidx[2][kTileRows];
-  unsigned long long cand[2][kTileRows];
-  float rmin[kTileRows];
-  float band[kTileRows];
-  int ambiguous[kTileRows];
-  float cmax_w[kThreads / 32];
-  uint64_t mma_done;
+  uint8_t a_ops[2][kOpBytes];      // query tile hi | lo (each 1024-B aligned)
+  float stage[kTileRows * kD];     // raw fp32 rows of the NEXT tile, filled asynchronously with cp.async (64 KB)
+  uint8_t b_ops[2][kOpBytes];      // codebook hi | lo
+  float sc2[kK];                   // |c_j|^2 (fp32, deterministic order)
+  float sx2[4][kTileRows];         // |x_r|^2, ring of 4 tiles (only used for the error band)
+  float cmax_w[8];
+  uint64_t a_full, a_empty, t_full[2], t_empty[2];
   uint32_t tmem_base;
-  int n_amb;
 };
 
 __device__ __forceinline__ void split_store(uint8_t* hi_tile, uint8_t* lo_tile, uint32_t off, const float (&v)[8]) {
@@ -61,6 +56,19 @@ __device__ __forceinline__ void split_store(uint8_t* hi_tile, uint8_t* lo_tile, 
   }
   *reinterpret_cast<uint4*>(hi_tile + off) = make_uint4(h[0], h[1], h[2], h[3]);
   *reinterpret_cast<uint4*>(lo_tile + off) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// 4 consecutive fp32 -> hi / lo bf16 pairs at element k0 of row r (K-major SW128 tile of two 64-col atoms)
+__device__ __forceinline__ void split_store4(uint8_t* hi_tile, uint8_t* lo_tile, int r, int k0, const float4& c) {
+  __nv_bfloat16 h0 = __float2bfloat16_rn(c.x), h1 = __float2bfloat16_rn(c.y), h2 = __float2bfloat16_rn(c.z),
+                h3 = __float2bfloat16_rn(c.w);
+  __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
+  const uint2 hi = make_uint2(*reinterpret_cast<uint32_t*>(&a0), *reinterpret_cast<uint32_t*>(&a1));
+  const uint2 lo = make_uint2(pt::pack_bf16x2(c.x - __bfloat162float(h0), c.y - __bfloat162float(h1)),
+                              pt::pack_bf16x2(c.z - __bfloat162float(h2), c.w - __bfloat162float(h3)));
+  const uint32_t off = (k0 >> 6) * kAtomBytes + pt::sw128_offset(r, (k0 & 63) >> 3) + (k0 & 7) * 2;
+  *reinterpret_cast<uint2*>(hi_tile + off) = hi;
+  *reinterpret_cast<uint2*>(lo_tile + off) = lo;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -78,8 +86,8 @@ struct PqArgs {
   float* gap_out;               // [B*W, G] or null
   float* score_dump;            // [B*W, G, 128] or null (test hook)
   int* n_rescored;              // single counter or null (test hook)
-  int rows_per_tile;
-  int rows_fast;                 // 1: channels-last rows, 16-byte aligned -> float4 row loader
+  int rows_per_tile, n_tiles, ctas_per_group;
+  int rows_fast;                // 1: channels-last rows, 16-byte aligned -> float4 row loader
 };
 
 template <bool kDump>
@@ -87,32 +95,53 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   extern __shared__ uint8_t smem_raw[];
   PqSmem& s = *reinterpret_cast<PqSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = blockIdx.y;
+  const int g = blockIdx.x / a.ctas_per_group, part = blockIdx.x % a.ctas_per_group;
   const long long total_rows = (long long)a.B * a.W;
-  const long long row0 = (long long)blockIdx.x * a.rows_per_tile;
-  const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
   const float* cb = a.codebooks + (size_t)g * kK * kD;
+  const int W = a.W;
 
-  if (warp == 0) {
-    pt::tmem_alloc(&s.tmem_base, 128);
+  if (warp == kLoadWarps) {                       // the MMA warp also owns TMEM
+    pt::tmem_alloc(&s.tmem_base, 256);
     pt::tmem_relinquish();
   }
   if (tid == 0) {
-    pt::mbar_init(&s.mma_done, 1);
+    pt::mbar_init(&s.a_full, kLoadWarps); pt::mbar_init(&s.a_empty, 1);
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&s.t_full[i], 1); pt::mbar_init(&s.t_empty[i], kScanWarps); }
     pt::fence_mbar_init();
-    s.n_amb = 0;
   }
-  if (tid < kTileRows) s.sx2[tid] = 0.f;
-  __syncthreads();
-
-  // ---- stage the codebook: warp per code row, lane holds k = 4*lane .. 4*lane+3 (coalesced 512 B).
-  // All 16 rows of a warp are requested before any is consumed (memory-level parallelism).
-  {
-    constexpr int kPerWarp = kK / (kThreads / 32);
+  // the first tile's rows start streaming before anything else happens
+  auto prefetch = [&](int t) {
+    const long long row0 = (long long)t * a.rows_per_tile;
+    const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
+    const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
+    if (a.rows_fast) {
+      // channels-last: stage[r][k], 16-byte copies, a warp covers one 512-byte row per instruction
+      for (int r = warp; r < nrows; r += kLoadWarps) {
+        const int q = w0 + r, b = b0 + q / W, w = q % W;
+        const float* src = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD + lane * 4;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pt::smem_u32(&s.stage[r * kD + lane * 4])), "l"(src) : "memory");
+      }
+    } else {
+      // channel-first: stage[k][r], 4-byte copies, lanes = consecutive rows (w contiguous in memory)
+      const int r = tid;
+      if (r < nrows) {
+        const int q = w0 + r, b = b0 + q / W, w = q % W;
+        const float* prow = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
+#pragma unroll 8
+        for (int k = 0; k < kD; ++k)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(pt::smem_u32(&s.stage[k * kTileRows + r])), "l"(prow + (size_t)k * a.zs_c) : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (warp < kLoadWarps && part < a.n_tiles) prefetch(part);
+  // ---- prologue: stage the codebook once (warps 0-7: 16 code rows each, all loads in flight before any is used)
+  if (warp < 8) {
+    constexpr int kPerWarp = kK / 8;
     float4 cv[kPerWarp];
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i)
-      cv[i] = __ldg(reinterpret_cast<const float4*>(cb + (size_t)(warp + i * (kThreads / 32)) * kD) + lane);
+      cv[i] = __ldg(reinterpret_cast<const float4*>(cb + (size_t)(warp + i * 8) * kD) + lane);
     float sq[kPerWarp];
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i)
@@ -120,229 +149,213 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-      for (int i = 0; i < kPerWarp; ++i) sq[i] += __shfl_xor_sync(0xffffffffu, sq[i], o);   // 16 independent chains
+      for (int i = 0; i < kPerWarp; ++i) sq[i] += __shfl_xor_sync(0xffffffffu, sq[i], o);
     }
     float wmax = 0.f;
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i) {
-      const int j = warp + i * (kThreads / 32);
-      const float4 c = cv[i];
+      const int j = warp + i * 8;
       wmax = fmaxf(wmax, sq[i]);
       if (lane == 0) s.sc2[j] = sq[i];
-      __nv_bfloat16 h0 = __float2bfloat16_rn(c.x), h1 = __float2bfloat16_rn(c.y), h2 = __float2bfloat16_rn(c.z),
-                    h3 = __float2bfloat16_rn(c.w);
-      __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
-      uint2 hi = make_uint2(*reinterpret_cast<uint32_t*>(&a0), *reinterpret_cast<uint32_t*>(&a1));
-      uint2 lo = make_uint2(pt::pack_bf16x2(c.x - __bfloat162float(h0), c.y - __bfloat162float(h1)),
-                            pt::pack_bf16x2(c.z - __bfloat162float(h2), c.w - __bfloat162float(h3)));
-      const int k0 = lane * 4;                       // element index within the row
-      const uint32_t off = (k0 >> 6) * kAtomBytes + pt::sw128_offset(j, (k0 & 63) >> 3) + (k0 & 7) * 2;
-      *reinterpret_cast<uint2*>(s.ops[2] + off) = hi;
-      *reinterpret_cast<uint2*>(s.ops[3] + off) = lo;
+      split_store4(s.b_ops[0], s.b_ops[1], j, lane * 4, cv[i]);
     }
     if (lane == 0) s.cmax_w[warp] = sqrtf(wmax);
   }
-
-  // ---- stage the query rows (row index math in 32 bits: tiles never span more than 2^31 rows)
-  const int W = a.W;
-  const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
-  if (a.rows_fast) {
-    // channels-last rows: warp per row, float4 per lane; 16 rows in flight per warp
-    constexpr int kPerWarp = kTileRows / (kThreads / 32);
-    float4 xv[kPerWarp];
-#pragma unroll
-    for (int i = 0; i < kPerWarp; ++i) {
-      const int r = warp + i * (kThreads / 32);
-      xv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (r < nrows) {
-        const int q = w0 + r, b = b0 + q / W, w = q % W;
-        xv[i] = __ldg(reinterpret_cast<const float4*>(a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD) + lane);
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < kPerWarp; ++i) {
-      const int r = warp + i * (kThreads / 32);
-      const float4 x = xv[i];
-      float sq = warp_sum(fmaf(x.w, x.w, fmaf(x.z, x.z, fmaf(x.y, x.y, x.x * x.x))));
-      if (lane == 0) s.sx2[r] = sq;
-      __nv_bfloat16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y), h2 = __float2bfloat16_rn(x.z),
-                    h3 = __float2bfloat16_rn(x.w);
-      __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
-      uint2 hi = make_uint2(*reinterpret_cast<uint32_t*>(&a0), *reinterpret_cast<uint32_t*>(&a1));
-      uint2 lo = make_uint2(pt::pack_bf16x2(x.x - __bfloat162float(h0), x.y - __bfloat162float(h1)),
-                            pt::pack_bf16x2(x.z - __bfloat162float(h2), x.w - __bfloat162float(h3)));
-      const int k0 = lane * 4;
-      const uint32_t off = (k0 >> 6) * kAtomBytes + pt::sw128_offset(r, (k0 & 63) >> 3) + (k0 & 7) * 2;
-      *reinterpret_cast<uint2*>(s.ops[0] + off) = hi;
-      *reinterpret_cast<uint2*>(s.ops[1] + off) = lo;
-    }
-  } else {
-    // channel-first (the reference's [B, C, W]): lanes walk consecutive rows (w contiguous), 8 channels per
-    // unit; a thread's units share its row, and 4 units (32 loads) are in flight at a time
-    const int r = tid & (kTileRows - 1);
-    const bool live = r < nrows;
-    const int q = w0 + r, b = b0 + q / W, w = q % W;
-    const float* prow = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
-    float sq = 0.f;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      float v[4][8];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int chunk = (tid >> 7) + 2 * (h * 4 + u);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[u][i] = live ? __ldg(prow + (size_t)(chunk * 8 + i) * a.zs_c) : 0.f;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int chunk = (tid >> 7) + 2 * (h * 4 + u);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) sq = fmaf(v[u][i], v[u][i], sq);
-        const uint32_t off = (chunk >> 3) * kAtomBytes + pt::sw128_offset(r, chunk & 7);
-        split_store(s.ops[0], s.ops[1], off, v[u]);
-      }
-    }
-    if (live) atomicAdd(&s.sx2[r], sq);
-  }
-  pt::fence_async_smem();        // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+  pt::fence_async_smem();
   pt::tc_fence_before();
   __syncthreads();
   pt::tc_fence_after();
   const uint32_t tmem = s.tmem_base;
 
-  // ---- 24 MMAs by one thread: D = Ahi*Bhi^T + Ahi*Blo^T + Alo*Bhi^T
-  if (tid == 0) {
-    const uint32_t idesc = pt::umma_idesc_bf16(128, 128);
-    const uint32_t a_hi = pt::smem_u32(s.ops[0]), a_lo = pt::smem_u32(s.ops[1]);
-    const uint32_t b_hi = pt::smem_u32(s.ops[2]), b_lo = pt::smem_u32(s.ops[3]);
-    const uint32_t pa[3] = {a_hi, a_hi, a_lo}, pb[3] = {b_hi, b_lo, b_hi};
-    uint32_t acc = 0;
-#pragma unroll
-    for (int p = 0; p < 3; ++p) {
-#pragma unroll
-      for (int k = 0; k < kD / 16; ++k) {
-        const uint32_t koff = (k >> 2) * kAtomBytes + (k & 3) * 32;
-        pt::umma_bf16(tmem, pt::umma_desc_sw128(pa[p] + koff), pt::umma_desc_sw128(pb[p] + koff), idesc, acc);
-        acc = 1;
-      }
-    }
-    pt::umma_commit(&s.mma_done);
-  }
-  pt::mbar_wait(&s.mma_done, 0);
-  pt::tc_fence_after();
-
-  // ---- scan: warp w reads TMEM lanes 32*(w%4).., columns 64*(w/4)..+63
-  const int r = (warp & 3) * 32 + lane;
-  const int half = warp >> 2;
-  const uint32_t t_row = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16) + half * 64;
-  // two independent (min, argmin, second-min) trackers (even / odd columns) for instruction-level parallelism
-  float ma1 = INFINITY, ma2 = INFINITY, mb1 = INFINITY, mb2 = INFINITY;
-  int ia = 0, ib = 1;
-#pragma unroll
-  for (int c = 0; c < 2; ++c) {
-    uint32_t v[32];
-    pt::tmem_ld32(t_row + c * 32, v);
-    pt::tmem_ld_wait();
-#pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-      const int j = half * 64 + c * 32 + i;
-      const float sa = fmaf(-2.f, __uint_as_float(v[i]), s.sc2[j]);
-      const float sb = fmaf(-2.f, __uint_as_float(v[i + 1]), s.sc2[j + 1]);
-      if constexpr (kDump) {
-        if (r < nrows) {
-          a.score_dump[((row0 + r) * a.G + g) * kK + j] = sa;
-          a.score_dump[((row0 + r) * a.G + g) * kK + j + 1] = sb;
+  if (warp < kLoadWarps) {
+    // ------------------------------------------------------------ loaders
+    // The raw fp32 rows of tile t+1 stream into `stage` with cp.async (no registers, thousands of bytes in flight)
+    // while tile t is in the tensor core; once they have landed and the MMA has released the operand buffer they are
+    // split into hi / lo bf16 and written K-major, SWIZZLE_128B.
+    int it = 0;
+    for (int t = part; t < a.n_tiles; t += a.ctas_per_group, ++it) {
+      const uint32_t ph = (uint32_t)it & 1u;
+      const long long row0 = (long long)t * a.rows_per_tile;
+      const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      asm volatile("bar.sync 1, 128;" ::: "memory");        // every loader thread's copies have landed
+      pt::mbar_wait(&s.a_empty, ph ^ 1);                    // the MMAs of the previous tile have read the operands
+      uint8_t* hi = s.a_ops[0];
+      uint8_t* lo = s.a_ops[1];
+      float* sx2 = s.sx2[it & 3];        // 4-deep: a slot is rewritten only after the scan of that tile has retired
+      if (a.rows_fast) {
+#pragma unroll 4
+        for (int r = warp; r < kTileRows; r += kLoadWarps) {
+          float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (r < nrows) x = *reinterpret_cast<const float4*>(&s.stage[r * kD + lane * 4]);
+          const float sq = warp_sum(fmaf(x.w, x.w, fmaf(x.z, x.z, fmaf(x.y, x.y, x.x * x.x))));
+          if (lane == 0) sx2[r] = sq;
+          split_store4(hi, lo, r, lane * 4, x);
         }
+      } else {
+        const int r = tid;
+        const bool live = r < nrows;
+        float sq = 0.f;
+#pragma unroll 4
+        for (int chunk = 0; chunk < 16; ++chunk) {
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = live ? s.stage[(chunk * 8 + i) * kTileRows + r] : 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) sq = fmaf(v[i], v[i], sq);
+          split_store(hi, lo, (chunk >> 3) * kAtomBytes + pt::sw128_offset(r, chunk & 7), v);
+        }
+        sx2[r] = sq;
       }
-      ma2 = fminf(ma2, fmaxf(sa, ma1));           // second-min update, then min (strict < keeps the first index)
-      if (sa < ma1) { ma1 = sa; ia = j; }
-      mb2 = fminf(mb2, fmaxf(sb, mb1));
-      if (sb < mb1) { mb1 = sb; ib = j + 1; }
+      pt::fence_async_smem();                                // generic-proxy smem writes -> tensor-core proxy
+      asm volatile("bar.sync 1, 128;" ::: "memory");        // everyone is done reading `stage`
+      if (lane == 0) pt::mbar_arrive(&s.a_full);
+      const int nt = t + a.ctas_per_group;
+      if (nt < a.n_tiles) prefetch(nt);
     }
-  }
-  // merge the trackers; on equal scores the smaller index wins
-  float m1, m2;
-  int i1;
-  if (mb1 < ma1 || (mb1 == ma1 && ib < ia)) { m1 = mb1; i1 = ib; m2 = fminf(ma1, mb2); }
-  else { m1 = ma1; i1 = ia; m2 = fminf(mb1, ma2); }
-  s.pmin[half][r] = m1; s.pmin2[half][r] = m2; s.pidx[half][r] = i1;
-  __syncthreads();
-  bool amb = false;
-  if (half == 0) {
-    float n1 = s.pmin[1][r], n2 = s.pmin2[1][r];
-    int k1 = s.pidx[1][r];
-    // merge halves; the low half wins ties (first minimum, like torch.argmin)
-    float best = m1, second = fminf(m2, n1);
-    int bi = i1;
-    if (n1 < m1) { best = n1; bi = k1; second = fminf(m1, n2); }
+  } else if (warp == kLoadWarps) {
+    // ------------------------------------------------------------ MMA issuer: D = Ahi*Bhi^T + Ahi*Blo^T + Alo*Bhi^T
+    if (lane == 0) {
+      const uint32_t idesc = pt::umma_idesc_bf16(128, 128);
+      const uint32_t b_hi = pt::smem_u32(s.b_ops[0]), b_lo = pt::smem_u32(s.b_ops[1]);
+      int it = 0;
+      for (int t = part; t < a.n_tiles; t += a.ctas_per_group, ++it) {
+        const int buf = it & 1;                              // TMEM accumulator stage
+        const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+        pt::mbar_wait(&s.a_full, (uint32_t)it & 1u);
+        pt::mbar_wait(&s.t_empty[buf], ph ^ 1);
+        pt::tc_fence_after();
+        const uint32_t a_hi = pt::smem_u32(s.a_ops[0]), a_lo = pt::smem_u32(s.a_ops[1]);
+        const uint32_t pa[3] = {a_hi, a_hi, a_lo}, pb[3] = {b_hi, b_lo, b_hi};
+        uint32_t acc = 0;
+#pragma unroll
+        for (int p = 0; p < 3; ++p) {
+#pragma unroll
+          for (int k = 0; k < kD / 16; ++k) {
+            const uint32_t koff = (k >> 2) * kAtomBytes + (k & 3) * 32;
+            pt::umma_bf16(tmem + buf * 128, pt::umma_desc_sw128(pa[p] + koff), pt::umma_desc_sw128(pb[p] + koff), idesc, acc);
+            acc = 1;
+          }
+        }
+        pt::umma_commit(&s.t_full[buf]);
+        pt::umma_commit(&s.a_empty);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ scanners: thread = row, all 128 scores
+    const int qd = warp & 3;                                 // TMEM lane quadrant (== warp % 4)
+    const int r = qd * 32 + lane;
     float cmax = s.cmax_w[0];
 #pragma unroll
-    for (int i = 1; i < kThreads / 32; ++i) cmax = fmaxf(cmax, s.cmax_w[i]);
-    const float band = 2.f * kBand * sqrtf(s.sx2[r]) * cmax + 4e-7f * fabsf(best);
-    s.rmin[r] = best; s.band[r] = band;
-    amb = (r < nrows) && (second - best <= band);
-    s.ambiguous[r] = amb ? 1 : 0;
-    if (amb) atomicAdd(&s.n_amb, 1);
-    if (!amb && r < nrows) {
-      a.idx_out[(row0 + r) * a.G + g] = bi;
-      if (a.gap_out) a.gap_out[(row0 + r) * a.G + g] = second - best;
-    }
-  }
-  __syncthreads();
-  if (s.n_amb > 0) {                      // block-uniform
-    // second pass: candidate mask of every code inside the band (all warps re-read their columns)
-    const float lim = s.rmin[r] + s.band[r];
-    unsigned long long mask = 0ull;
+    for (int i = 1; i < 8; ++i) cmax = fmaxf(cmax, s.cmax_w[i]);
+    int it = 0;
+    for (int t = part; t < a.n_tiles; t += a.ctas_per_group, ++it) {
+      const int buf = it & 1;
+      const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+      const long long row0 = (long long)t * a.rows_per_tile;
+      const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
+      const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
+      pt::mbar_wait(&s.t_full[buf], ph);
+      pt::tc_fence_after();
+      const uint32_t t_row = tmem + buf * 128 + (static_cast<uint32_t>(qd * 32) << 16);
+      // two independent (min, argmin, second-min) trackers (even / odd columns) for instruction-level parallelism
+      float ma1 = INFINITY, ma2 = INFINITY, mb1 = INFINITY, mb2 = INFINITY;
+      int ia = 0, ib = 1;
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t v[32];
-      pt::tmem_ld32(t_row + c * 32, v);
-      pt::tmem_ld_wait();
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        pt::tmem_ld32(t_row + c * 32, v);
+        pt::tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float sc = fmaf(-2.f, __uint_as_float(v[i]), s.sc2[half * 64 + c * 32 + i]);
-        if (sc <= lim) mask |= 1ull << (c * 32 + i);
-      }
-    }
-    s.cand[half][r] = mask;
-    __syncthreads();
-    // fp32 re-score, warp per ambiguous row, lanes split k; reference formula (vqvae_modules.py:549-553)
-    for (int rr = warp; rr < nrows; rr += kThreads / 32) {
-      if (!s.ambiguous[rr]) continue;
-      const long long row = row0 + rr;
-      const int q = w0 + rr, b = b0 + q / W, w = q % W;
-      const float* px = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
-      float x[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) x[i] = __ldg(px + (size_t)(lane + 32 * i) * a.zs_c);
-      float sx2 = warp_sum(fmaf(x[3], x[3], fmaf(x[2], x[2], fmaf(x[1], x[1], x[0] * x[0]))));
-      float best = INFINITY, second = INFINITY;
-      int bi = 0;
-      for (int h = 0; h < 2; ++h) {
-        unsigned long long m = s.cand[h][rr];
-        while (m) {
-          const int j = h * 64 + __ffsll((long long)m) - 1;
-          m &= m - 1;
-          const float* pc = cb + (size_t)j * kD;
-          float dot = 0.f;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) dot = fmaf(x[i], __ldg(pc + lane + 32 * i), dot);
-          dot = warp_sum(dot);
-          const float d = (sx2 + s.sc2[j]) - 2.f * dot;
-          if (d < best) { second = best; best = d; bi = j; }      // ascending j: first minimum wins ties
-          else if (d < second) { second = d; }
+        for (int i = 0; i < 32; i += 2) {
+          const int j = c * 32 + i;
+          const float sa = fmaf(-2.f, __uint_as_float(v[i]), s.sc2[j]);
+          const float sb = fmaf(-2.f, __uint_as_float(v[i + 1]), s.sc2[j + 1]);
+          if constexpr (kDump) {
+            if (r < nrows) {
+              a.score_dump[((row0 + r) * a.G + g) * kK + j] = sa;
+              a.score_dump[((row0 + r) * a.G + g) * kK + j + 1] = sb;
+            }
+          }
+          ma2 = fminf(ma2, fmaxf(sa, ma1));          // second-min update, then min (strict < keeps the first index)
+          if (sa < ma1) { ma1 = sa; ia = j; }
+          mb2 = fminf(mb2, fmaxf(sb, mb1));
+          if (sb < mb1) { mb1 = sb; ib = j + 1; }
         }
       }
-      if (lane == 0) {
-        a.idx_out[row * a.G + g] = bi;
-        if (a.gap_out) a.gap_out[row * a.G + g] = second - best;
-        if (a.n_rescored) atomicAdd(a.n_rescored, 1);
+      // merge the trackers; on equal scores the smaller index wins (first minimum, like torch.argmin)
+      float best, second;
+      int bi;
+      if (mb1 < ma1 || (mb1 == ma1 && ib < ia)) { best = mb1; bi = ib; second = fminf(ma1, mb2); }
+      else { best = ma1; bi = ia; second = fminf(mb1, ma2); }
+      const float band = 2.f * kBand * sqrtf(s.sx2[it & 3][r]) * cmax + 4e-7f * fabsf(best);
+      const bool amb = (r < nrows) && (second - best <= band);
+      const unsigned amb_mask = __ballot_sync(0xffffffffu, amb);
+      unsigned cand[4] = {0u, 0u, 0u, 0u};
+      if (amb_mask) {                              // warp-uniform: second pass collects every code inside the band
+        const float lim = best + band;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          pt::tmem_ld32(t_row + c * 32, v);
+          pt::tmem_ld_wait();
+          unsigned m = 0u;
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (fmaf(-2.f, __uint_as_float(v[i]), s.sc2[c * 32 + i]) <= lim) m |= 1u << i;
+          cand[c] = m;
+        }
+      }
+      pt::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) pt::mbar_arrive(&s.t_empty[buf]);       // the accumulator may be overwritten from here on
+      if (!amb && r < nrows) {
+        a.idx_out[(row0 + r) * a.G + g] = bi;
+        if (a.gap_out) a.gap_out[(row0 + r) * a.G + g] = second - best;
+      }
+      // fp32 re-score of the ambiguous rows of this warp, one row at a time, lanes split k;
+      // reference formula (vqvae_modules.py:549-553)
+      unsigned todo = amb_mask;
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int rr = qd * 32 + src;
+        const long long row = row0 + rr;
+        const int q = w0 + rr, b = b0 + q / W, w = q % W;
+        const float* px = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
+        float x[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = __ldg(px + (size_t)(lane + 32 * i) * a.zs_c);
+        const float sx2 = warp_sum(fmaf(x[3], x[3], fmaf(x[2], x[2], fmaf(x[1], x[1], x[0] * x[0]))));
+        float rbest = INFINITY, rsecond = INFINITY;
+        int rbi = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          unsigned m = __shfl_sync(0xffffffffu, cand[c], src);
+          while (m) {
+            const int j = c * 32 + __ffs(m) - 1;
+            m &= m - 1;
+            const float* pc = cb + (size_t)j * kD;
+            float dot = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dot = fmaf(x[i], __ldg(pc + lane + 32 * i), dot);
+            dot = warp_sum(dot);
+            const float d = (sx2 + s.sc2[j]) - 2.f * dot;
+            if (d < rbest) { rsecond = rbest; rbest = d; rbi = j; }      // ascending j: first minimum wins ties
+            else if (d < rsecond) { rsecond = d; }
+          }
+        }
+        if (lane == 0) {
+          a.idx_out[row * a.G + g] = rbi;
+          if (a.gap_out) a.gap_out[row * a.G + g] = rsecond - rbest;
+          if (a.n_rescored) atomicAdd(a.n_rescored, 1);
+        }
       }
     }
   }
   pt::tc_fence_before();
   __syncthreads();
-  if (warp == 0) pt::tmem_dealloc(tmem, 128);
+  if (warp == kLoadWarps) pt::tmem_dealloc(tmem, 256);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -371,19 +384,6 @@ __global__ void pq_gather_kernel(const IdxT* __restrict__ idx, const float* __re
   }
 }
 
-int choose_rows_per_tile(long long rows, int G, int sms) {
-  // fewest waves first, then the smallest tile (tile time grows with its rows)
-  int best = kTileRows;
-  double best_cost = 1e30;
-  for (int R = 16; R <= kTileRows; R += 8) {
-    const long long units = ((rows + R - 1) / R) * G;
-    const long long waves = (units + sms - 1) / sms;
-    const double cost = (double)waves * (40.0 + R);     // ~40 rows' worth of fixed cost per tile (codebook, MMA, scan)
-    if (cost < best_cost - 1e-9) { best_cost = cost; best = R; }
-  }
-  return best;
-}
-
 }  // namespace
 
 extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long long zs_w, int B, int W, int G,
@@ -395,24 +395,34 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   if ((long long)B * W == 0) return 0;
   if (!z || !codebooks || !idx_out) return pt::fail("pt_pq_search: null pointer");
   if (reinterpret_cast<uintptr_t>(codebooks) & 15) return pt::fail("pt_pq_search: codebooks must be 16-byte aligned");
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = pt::sm_count();
   PqArgs a;
   a.z = z; a.zs_b = zs_b; a.zs_w = zs_w; a.zs_c = zs_c; a.B = B; a.W = W; a.G = G;
   a.codebooks = codebooks; a.idx_out = idx_out; a.gap_out = gap_out; a.score_dump = score_dump;
   a.n_rescored = n_rescored;
   a.rows_fast = (zs_c == 1 && !(reinterpret_cast<uintptr_t>(z) & 15) && !(zs_b & 3) && !(zs_w & 3)) ? 1 : 0;
   const long long rows = (long long)B * W;
-  a.rows_per_tile = choose_rows_per_tile(rows, G, sms);
+  // persistent CTAs: `per_group` CTAs per sub-codebook, each walking k tiles; tile height chosen so that the tiles
+  // divide evenly (a tile costs ~ its rows, so 2 x 77 rows beats 128 + 25)
+  int per_group = sms / G;
+  if (per_group < 1) per_group = 1;
+  const long long full_tiles = (rows + kTileRows - 1) / kTileRows;
+  if (full_tiles < per_group) per_group = (int)full_tiles;
+  const long long k = (full_tiles + per_group - 1) / per_group;            // tiles per CTA
+  long long R = (rows + k * per_group - 1) / (k * per_group);
+  R = (R + 7) / 8 * 8;
+  if (R > kTileRows) R = kTileRows;
+  a.rows_per_tile = (int)R;
+  a.n_tiles = (int)((rows + R - 1) / R);
+  a.ctas_per_group = per_group;
   const size_t smem = sizeof(PqSmem) + 1024;
-  static bool attr_done[64] = {};
-  if (!attr_done[dev & 63]) {
+  static bool attr_done = false;
+  if (!attr_done) {
     PT_CUDA(cudaFuncSetAttribute(pq_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     PT_CUDA(cudaFuncSetAttribute(pq_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done[dev & 63] = true;
+    attr_done = true;
   }
-  dim3 grid((unsigned)((rows + a.rows_per_tile - 1) / a.rows_per_tile), (unsigned)G);
+  const unsigned grid = (unsigned)(per_group * G);
   if (score_dump) pq_search_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
   else pq_search_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
   PT_CUDA(cudaGetLastError());

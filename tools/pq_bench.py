@@ -40,6 +40,16 @@ def main():
     us = e0.elapsed_time(e1) / iters * 1e3
     byts = z.numel() * 4 + cb.numel() * 4 + idx.numel() * 8
     print("pq_search B=%d layout=%s: %.2f us/launch, %.1f GB/s algorithmic (%.2f MB)" % (B, layout, us, byts / us / 1e3, byts / 1e6))
+    # device time without host launch cost: replay a CUDA graph of `iters` launches
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        st2 = torch.cuda.current_stream().cuda_stream
+        for _ in range(iters):
+            assert L.pt_pq_search(z.data_ptr(), sb, sc, sw, B, W, G, 128, 128, cb.data_ptr(), idx.data_ptr(), None, None, None, st2) == 0
+    g.replay(); torch.cuda.synchronize()
+    e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / iters * 1e3
+    print("   graph replay: %.2f us/launch, %.1f GB/s algorithmic" % (us, byts / us / 1e3))
 
 
 if __name__ == "__main__":
