@@ -46,8 +46,10 @@ def test_windows_demo_long_form(pipe):
     pipe.generator = torch.Generator(device="cuda").manual_seed(9)
     out, codes = pipe.windows_demo(aud, labels)
     assert out.shape == (B, 376, t) and bool(torch.isfinite(out).all())
-    n_win = len(D.demo_window_bounds(t, 180))
-    assert n_win == 4 and codes.shape == (B, 22 + 19 * (n_win - 1), 4)
+    wins = D.demo_window_bounds(t, 180)
+    steps = [((e - s_) // 2 // 2 // 2) for s_, e in wins]          # 180 -> 22 token steps, 150 -> 18
+    assert len(wins) == 4 and steps == [22, 22, 22, 18]
+    assert codes.shape == (B, steps[0] + sum(n - 3 for n in steps[1:]), 4)   # demo.py:151 drops 3 steps per later window
     assert int(codes.min()) >= 0 and int(codes.max()) < 128
     # deterministic for a fixed noise generator
     pipe.generator = torch.Generator(device="cuda").manual_seed(9)
