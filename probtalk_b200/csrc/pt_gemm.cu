@@ -32,12 +32,13 @@ constexpr int kEpiWarps = 8;
 constexpr int kThreads = (kEpiWarp0 + kEpiWarps) * 32;   // 384
 constexpr int kTilePitch = 80;                          // 64 B payload + 16 B pad: conflict-free 16-byte accesses
 
-template <int BN>
+template <int BN, bool k2 = false>
 struct Cfg {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  // k2 (cta_group::2): each CTA of a pair stages its 128 rows of A and HALF of the BN weight rows
   static constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
-  static constexpr uint32_t kBBytes = BN * BK * 2;          // 16 / 32 KB
+  static constexpr uint32_t kBBytes = (k2 ? BN / 2 : BN) * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (kStageBytes == 48 * 1024) ? 4 : 6;
   static constexpr uint32_t kTmemCols = 2 * BN;             // double-buffered accumulator
   static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256;   // + 24 KB static (epilogue staging)
 };
@@ -101,11 +102,14 @@ __device__ __forceinline__ void welford_merge(float& n, float& mean, float& m2, 
 // kCL > 1 (plain variant only): clusters of kCL CTAs along M work on kCL consecutive 128-row tiles of the SAME
 // column tile; every CTA loads 1/kCL of the weight box and multicasts it to the whole cluster, so weight traffic
 // from L2 drops by kCL (these GEMMs have K = 512..2048 and are L2-bandwidth bound with private weight loads).
-template <int BN, bool kRowNorm, int kCL>
+// k2: pairs of CTAs (cta_group::2) compute a 256-row x BN tile together: the leader's MMA thread issues
+// M = 256 instructions that read 128 A rows and BN/2 weight rows from EACH CTA's smem, so a CTA stages (and the tensor
+// core reads) half the weight bytes per FLOP; stages shrink to 32 KB and the ring deepens from 4 to 6.
+template <int BN, bool kRowNorm, int kCL, bool k2 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const GemmKernelArgs p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, k2>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)C::kStages * C::kStageBytes);
@@ -123,15 +127,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   static_assert(!(kRowNorm && kCL != 1), "row-norm clusters are along N");
-  constexpr int kClusterSize = kRowNorm ? 2 : kCL;
+  static_assert(!(k2 && (kRowNorm || kCL != 1)), "cta_group::2 is its own variant");
+  constexpr int kClusterSize = (kRowNorm || k2) ? 2 : kCL;
   const uint32_t rank = (kClusterSize > 1) ? cluster_ctarank() : 0u;
   const int tile_first = (int)(blockIdx.x / kClusterSize);
   const int tile_stride = (int)(gridDim.x / kClusterSize);
   // kRowNorm: one "tile" = a 128-row block (the two CTAs split its 512 columns);
   // kCL > 1 : one "tile" = kCL consecutive 128-row blocks x one column tile (CTA `rank` owns block rank)
-  const int m_super = (p.m_tiles + kCL - 1) / kCL;
+  constexpr int kRowBlocks = k2 ? 2 : kCL;             // 128-row blocks covered by one cluster step
+  const int m_super = (p.m_tiles + kRowBlocks - 1) / kRowBlocks;
   const int n_tiles_total = kRowNorm ? p.m_tiles : m_super * p.N_tiles;
-  auto tile_m0 = [&](int tile) { return kRowNorm ? tile * BM : ((tile / p.N_tiles) * kCL + (int)rank) * BM; };
+  auto tile_m0 = [&](int tile) { return kRowNorm ? tile * BM : ((tile / p.N_tiles) * kRowBlocks + (int)rank) * BM; };
   auto tile_n0 = [&](int tile) { return kRowNorm ? (int)rank * BN : (tile % p.N_tiles) * BN; };
   constexpr uint16_t kMcMask = (uint16_t)((1u << kCL) - 1u);
 
@@ -141,13 +147,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], kCL); }
-    for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], kEpiWarps); }
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], (k2 ? 2 : 1) * kEpiWarps); }
     if constexpr (kRowNorm) { pt::mbar_init(&stats_bar[0], 2 * kEpiWarps); pt::mbar_init(&stats_bar[1], 2 * kEpiWarps); }
     pt::fence_mbar_init();
   }
   if (warp == 2) {
-    pt::tmem_alloc(tmem_slot, C::kTmemCols);
-    pt::tmem_relinquish();
+    if constexpr (k2) { pt::tmem_alloc_2sm(tmem_slot, C::kTmemCols); pt::tmem_relinquish_2sm(); }
+    else { pt::tmem_alloc(tmem_slot, C::kTmemCols); pt::tmem_relinquish(); }
   }
   pt::tc_fence_before();
   __syncthreads();
@@ -165,6 +171,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           const int tap = kk / p.c_iters, cc = kk - tap * p.c_iters;
           pt::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+          if constexpr (k2) {
+            // both CTAs' boxes complete on the leader's barrier: the leader arms it for the pair's bytes
+            if (rank == 0) pt::mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+            pt::tma_load_2d_2sm(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
+            pt::tma_load_2d_2sm(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0 + (int)rank * (BN / 2));
+            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           pt::mbar_expect_tx(&full[stage], C::kStageBytes);
           pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
           if constexpr (kCL == 1) {
@@ -180,9 +194,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc = pt::umma_idesc_bf16(BM, BN);
+    // ------------------------------------------------------------ MMA issuer (k2: the leader CTA issues for the pair)
+    if (lane == 0 && (!k2 || rank == 0)) {
+      const uint32_t idesc = pt::umma_idesc_bf16(k2 ? 2 * BM : BM, BN);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
@@ -196,12 +210,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           const uint32_t sb = sa + C::kABytes;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
-                          (kk | k) ? 1u : 0u);
+            if constexpr (k2)
+              pt::umma_bf16_2sm(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
+                                (kk | k) ? 1u : 0u);
+            else
+              pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
+                            (kk | k) ? 1u : 0u);
           }
-          if constexpr (kCL == 1) pt::umma_commit(&empty[stage]);   // slot reusable once these MMAs have read it
-          else pt::umma_commit_mc(&empty[stage], kMcMask);          // ... in every CTA that multicasts into it
-          if (kk == p.K_iters - 1) pt::umma_commit(&tmem_full[acc]);
+          if constexpr (k2) {
+            pt::umma_commit_2sm(&empty[stage], 3);                  // both CTAs' slots are free
+            if (kk == p.K_iters - 1) pt::umma_commit_2sm(&tmem_full[acc], 3);   // both CTAs' accumulators are ready
+          } else {
+            if constexpr (kCL == 1) pt::umma_commit(&empty[stage]);   // slot reusable once these MMAs have read it
+            else pt::umma_commit_mc(&empty[stage], kMcMask);          // ... in every CTA that multicasts into it
+            if (kk == p.K_iters - 1) pt::umma_commit(&tmem_full[acc]);
+          }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -221,6 +244,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     const bool row_major = (p.ocs == 1);
     const bool gate = (p.act == PT_ACT_GATE);
     const int pr = lane >> 2, pc = lane & 3;             // piece mapping: row pr + 8*j, 16-byte piece pc
+    // release an accumulator stage to the MMA issuer (k2: the issuer lives in the leader CTA)
+    auto release_acc = [&](int acc_stage) {
+      if constexpr (k2) {
+        if (rank == 0) pt::mbar_arrive(&tmem_empty[acc_stage]);
+        else asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];"
+                          ::"r"(map_to_peer(&tmem_empty[acc_stage], 0u)) : "memory");
+      } else {
+        pt::mbar_arrive(&tmem_empty[acc_stage]);
+      }
+    };
     // f[0..31] += residual[row, n .. n+31] (bf16, row-major): coalesced 64-byte row segments -> smem tile -> own row
     auto add_residual_bf16 = [&](float (&f)[32], int n) {
       __syncwarp();
@@ -372,7 +405,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         }
         pt::tc_fence_before();
         __syncwarp();
-        if (lane == 0) pt::mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) release_acc(acc);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         continue;
       }
@@ -516,14 +549,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       }
       pt::tc_fence_before();
       __syncwarp();
-      if (lane == 0) pt::mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) release_acc(acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
   pt::tc_fence_before();
   __syncthreads();
   if constexpr (kClusterSize > 1) cluster_sync_all();  // no CTA exits while a peer may still write into its smem
-  if (warp == 2) pt::tmem_dealloc(tmem_base, C::kTmemCols);
+  if (warp == 2) {
+    if constexpr (k2) pt::tmem_dealloc_2sm(tmem_base, C::kTmemCols);
+    else pt::tmem_dealloc(tmem_base, C::kTmemCols);
+  }
 }
 
 // ------------------------------------------------------------------ host side
@@ -586,6 +622,30 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& k
     cfg.attrs = attr; cfg.numAttrs = 1;
     PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, ka));
   }
+  return 0;
+}
+
+// cta_group::2 variant: pairs of CTAs, one 256-row x 256-column tile per pair step
+int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+  using Cf = Cfg<256, true>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, false, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cf::kSmem));
+    attr_done = true;
+  }
+  const int tiles = ((ka.m_tiles + 1) / 2) * ka.N_tiles;
+  int pairs = sms / 2;
+  if (tiles < pairs) pairs = tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = Cf::kSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, false, 1, true>, ta, tb, ka));
   return 0;
 }
 
@@ -656,8 +716,12 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     if ((reinterpret_cast<uintptr_t>(d->norm_a) | reinterpret_cast<uintptr_t>(d->norm_b)) & 15)
       return pt::fail("pt_gemm_bf16: norm tables must be 16-byte aligned");
   }
-  const int BN = d->row_norm ? 256
-               : (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
+  int BN = d->row_norm ? 256
+           : (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
+  {
+    const char* e = getenv("PT_GEMM_BN");                 // developer override: force 128-column tiles
+    if (e && !d->row_norm && atoi(e) == 128) BN = 128;
+  }
   // Weight multicast across clusters of CTAs along M (CL = 2 / 4) is implemented and tested, but measured no
   // faster than private loads on B200 (CL = 2: +2 %, CL = 4: -40 %, profiles/r01_notes.md): these GEMMs are bound by
   // the bytes in flight per SM, not by L2 bandwidth.  Default off.
@@ -666,7 +730,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     const char* e = getenv("PT_GEMM_CLUSTER");            // developer override (1, 2 or 4)
     if (e && !d->row_norm && BN == 256) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) CL = v; }
   }
-  if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, BN / CL)) return 1;
+  // cta_group::2 pairs for the big plain GEMMs (PT_GEMM_2CTA=0 disables, for A/B measurements)
+  bool two_cta = false;
+  {
+    static const bool off = getenv("PT_GEMM_2CTA") && atoi(getenv("PT_GEMM_2CTA")) == 0;
+    two_cta = !off && !d->row_norm && BN == 256 && CL == 1 &&
+              ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= 2LL * sms;
+  }
+  if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, two_cta ? 128 : BN / CL)) return 1;
 
   GemmKernelArgs ka;
   ka.M = d->M; ka.N_tiles = d->N / BN; ka.c_iters = d->C / BK; ka.K_iters = d->taps * ka.c_iters;
@@ -678,6 +749,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   ka.row_norm = d->row_norm; ka.norm_a = d->norm_a; ka.norm_b = d->norm_b; ka.labels = d->labels; ka.label_rows = d->label_rows;
   cudaStream_t st = (cudaStream_t)stream;
   if (d->row_norm) return launch_rownorm(ta, tb, ka, sms, st);
+  if (two_cta) return launch_2cta(ta, tb, ka, sms, st);
   if (BN == 128) return launch<128, 1>(ta, tb, ka, sms, st);
   if (CL == 4) return launch<256, 4>(ta, tb, ka, sms, st);
   if (CL == 2) return launch<256, 2>(ta, tb, ka, sms, st);

@@ -14,7 +14,8 @@ def _st():
     return torch.cuda.current_stream().cuda_stream
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1000, 256, 512), (333, 384, 1024), (4100, 1536, 512), (50, 2048, 512)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1000, 256, 512), (333, 384, 1024), (4100, 1536, 512), (50, 2048, 512),
+                                   (19000, 1024, 512), (40000, 512, 2048)])      # the last two take the cta_group::2 path
 @pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
 def test_gemm_plain(M, N, K, out_dtype):
     from probtalk_b200 import ops
