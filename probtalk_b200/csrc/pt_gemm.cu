@@ -30,7 +30,9 @@ constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
 constexpr int kEpiWarp0 = 4;
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = (kEpiWarp0 + kEpiWarps) * 32;   // 384
-constexpr int kTilePitch = 80;                          // 64 B payload + 16 B pad: conflict-free 16-byte accesses
+// epilogue staging tile: 32 rows x 64 B, 16-byte pieces XOR-swizzled by the row pair so that both access patterns
+// (thread = row writes its 4 pieces; 4 lanes x 8 rows read / write global 64-byte segments) are bank-conflict free
+#define PT_TILE_OFF(r, piece) ((r) * 64 + ((((piece) ^ ((r) >> 1)) & 3) << 4))
 
 template <int BN, bool k2 = false>
 struct Cfg {
@@ -120,7 +122,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   // epilogue staging lives in STATIC shared memory so the compiler emits LDS/STS (pointers carved from the
   // dynamic buffer lose their address space and become slow generic loads)
-  __shared__ __align__(16) uint8_t tile_s[kEpiWarps][32 * kTilePitch];
+  __shared__ __align__(16) uint8_t tile_s[kEpiWarps][32 * 64];
+  __shared__ __align__(16) float bias_s[kEpiWarps][BN / 2];      // this warp's 128 (or 64) bias columns of the current tile
   __shared__ long long rowoff_s[kEpiWarps][64];
   __shared__ float2 stats_s[kRowNorm ? 2 : 1][4][kRowNorm ? BM : 1];    // [tile parity][source warp-column][row] (mean, M2)
   __shared__ uint64_t stats_bar[2];
@@ -237,7 +240,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // covers whole 64-byte row segments (4 lanes x 16 B per row) instead of 32 different cache lines.
     const int e = warp - kEpiWarp0;
     const int q = e & 3, half = e >> 2;                  // TMEM lane quadrant (== warp % 4) and column half
-    uint8_t* tile = tile_s[e];                           // [32][kTilePitch] bytes
+    uint8_t* tile = tile_s[e];                           // [32 rows][4 swizzled 16-byte pieces]
     long long* row_out = rowoff_s[e];                    // [32] output row offsets (or -1), [32] residual offsets
     long long* row_res = rowoff_s[e] + 32;
     int acc = 0; uint32_t acc_phase = 0;
@@ -254,30 +257,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         pt::mbar_arrive(&tmem_empty[acc_stage]);
       }
     };
-    // f[0..31] += residual[row, n .. n+31] (bf16, row-major): coalesced 64-byte row segments -> smem tile -> own row
-    auto add_residual_bf16 = [&](float (&f)[32], int n) {
-      __syncwarp();
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int rr = pr + 8 * j;
-        uint4 x = make_uint4(0, 0, 0, 0);
-        if (row_out[rr] >= 0 && n + pc * 8 < p.n_valid)
-          x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + row_res[rr] + n) + pc);
-        *reinterpret_cast<uint4*>(tile + rr * kTilePitch + pc * 16) = x;
-      }
-      __syncwarp();
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const uint4 x = *reinterpret_cast<const uint4*>(tile + lane * kTilePitch + i * 16);
-        const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&w4[j]);
-          f[8 * i + 2 * j] += __bfloat162float(hh.x);
-          f[8 * i + 2 * j + 1] += __bfloat162float(hh.y);
-        }
-      }
-    };
     int it = 0;
     for (int tile_i = tile_first; tile_i < n_tiles_total; tile_i += tile_stride, ++it) {
       const int m0 = tile_m0(tile_i), n0 = tile_n0(tile_i);
@@ -288,7 +267,40 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       __syncwarp();
       row_out[lane] = row_ok ? obase : -1;
       row_res[lane] = (long long)b * p.rss + (long long)t * p.rrs;
+      // this warp's bias columns of the tile go to smem now, so their latency hides behind the accumulator wait
+      float* bias_w = bias_s[e];
+      if (p.bias) {
+        if (lane < BN / 8)
+          *reinterpret_cast<float4*>(bias_w + lane * 4) = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + half * (BN / 2)) + lane);
+      }
       __syncwarp();
+      long long ro4[4], rs4[4];                            // offsets of the rows this lane moves to / from global memory
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { ro4[j] = row_out[pr + 8 * j]; rs4[j] = row_res[pr + 8 * j]; }
+      // f[0..31] += residual[row, n .. n+31] (bf16, row-major): coalesced 64-byte row segments -> smem tile -> own row
+      auto add_residual_bf16 = [&](float (&f)[32], int n) {
+        __syncwarp();
+  #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int rr = pr + 8 * j;
+          uint4 x = make_uint4(0, 0, 0, 0);
+          if (ro4[j] >= 0 && n + pc * 8 < p.n_valid)
+            x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rs4[j] + n) + pc);
+          *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(rr, pc)) = x;
+        }
+        __syncwarp();
+  #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 x = *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(lane, i));
+          const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+  #pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&w4[j]);
+            f[8 * i + 2 * j] += __bfloat162float(hh.x);
+            f[8 * i + 2 * j + 1] += __bfloat162float(hh.y);
+          }
+        }
+      };
       pt::mbar_wait(&tmem_full[acc], acc_phase);
       pt::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
@@ -304,7 +316,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           float f[32];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n) + i);
+            const float4 bb = *reinterpret_cast<const float4*>(bias_w + (c0 - half * (BN / 2)) + 4 * i);
             f[4 * i] = __uint_as_float(v[4 * i]) + bb.x; f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + bb.y;
             f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + bb.z; f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bb.w;
           }
@@ -364,7 +376,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           float f[32];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n) + i);
+            const float4 bb = *reinterpret_cast<const float4*>(bias_w + (c0 - half * (BN / 2)) + 4 * i);
             f[4 * i] = __uint_as_float(v[4 * i]) + bb.x; f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + bb.y;
             f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + bb.z; f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bb.w;
           }
@@ -390,17 +402,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<uint4*>(tile + lane * kTilePitch + i * 16) = make_uint4(
+            *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, i)) = make_uint4(
                 pt::pack_bf16x2(f[8 * i], f[8 * i + 1]), pt::pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
                 pt::pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pt::pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int rr = pr + 8 * j;
-            const long long ro = row_out[rr];
+            const long long ro = ro4[j];
             if (ro >= 0)
               *(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + n) + pc) =
-                  *reinterpret_cast<const uint4*>(tile + rr * kTilePitch + pc * 16);
+                  *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pc));
           }
         }
         pt::tc_fence_before();
@@ -422,7 +434,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         if (p.bias) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n) + i);
+            const float4 bb = *reinterpret_cast<const float4*>(bias_w + (c0 - half * (BN / 2)) + 4 * i);
             f[4 * i] += bb.x; f[4 * i + 1] += bb.y; f[4 * i + 2] += bb.z; f[4 * i + 3] += bb.w;
           }
         }
@@ -451,14 +463,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
               for (int j = 0; j < 4; ++j) {
                 const int rr = pr + 8 * j;
                 float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (row_out[rr] >= 0 && n + h2 * 16 + pc * 4 < p.n_valid)
-                  x = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + row_res[rr] + n + h2 * 16) + pc);
-                *reinterpret_cast<float4*>(tile + rr * kTilePitch + pc * 16) = x;
+                if (ro4[j] >= 0 && n + h2 * 16 + pc * 4 < p.n_valid)
+                  x = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + rs4[j] + n + h2 * 16) + pc);
+                *reinterpret_cast<float4*>(tile + PT_TILE_OFF(rr, pc)) = x;
               }
               __syncwarp();
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const float4 x = *reinterpret_cast<const float4*>(tile + lane * kTilePitch + i * 16);
+                const float4 x = *reinterpret_cast<const float4*>(tile + PT_TILE_OFF(lane, i));
                 f[h2 * 16 + 4 * i] += x.x; f[h2 * 16 + 4 * i + 1] += x.y; f[h2 * 16 + 4 * i + 2] += x.z; f[h2 * 16 + 4 * i + 3] += x.w;
               }
             }
@@ -468,14 +480,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             for (int j = 0; j < 4; ++j) {
               const int rr = pr + 8 * j;
               uint4 x = make_uint4(0, 0, 0, 0);
-              if (row_out[rr] >= 0 && n + pc * 8 < p.n_valid)
-                x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + row_res[rr] + n) + pc);
-              *reinterpret_cast<uint4*>(tile + rr * kTilePitch + pc * 16) = x;
+              if (ro4[j] >= 0 && n + pc * 8 < p.n_valid)
+                x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rs4[j] + n) + pc);
+              *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(rr, pc)) = x;
             }
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-              const uint4 x = *reinterpret_cast<const uint4*>(tile + lane * kTilePitch + i * 16);
+              const uint4 x = *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(lane, i));
               const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
@@ -497,8 +509,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             g8[i] = pt::pack_bf16x2(g0, g1);
           }
           __syncwarp();
-          *reinterpret_cast<uint4*>(tile + lane * kTilePitch) = make_uint4(g8[0], g8[1], g8[2], g8[3]);
-          *reinterpret_cast<uint4*>(tile + lane * kTilePitch + 16) = make_uint4(g8[4], g8[5], g8[6], g8[7]);
+          *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, 0)) = make_uint4(g8[0], g8[1], g8[2], g8[3]);
+          *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, 1)) = make_uint4(g8[4], g8[5], g8[6], g8[7]);
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
@@ -506,7 +518,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             const long long ro = row_out[rr];
             if (ro >= 0)
               *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + (n >> 1) + pp * 8) =
-                  *reinterpret_cast<const uint4*>(tile + rr * kTilePitch + pp * 16);
+                  *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pp));
           }
         } else if (p.out_f32) {
 #pragma unroll
@@ -514,24 +526,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-              *reinterpret_cast<float4*>(tile + lane * kTilePitch + i * 16) =
+              *reinterpret_cast<float4*>(tile + PT_TILE_OFF(lane, i)) =
                   make_float4(apply_act(f[h2 * 16 + 4 * i], p.act, p.slope), apply_act(f[h2 * 16 + 4 * i + 1], p.act, p.slope),
                               apply_act(f[h2 * 16 + 4 * i + 2], p.act, p.slope), apply_act(f[h2 * 16 + 4 * i + 3], p.act, p.slope));
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               const int rr = pr + 8 * j;
-              const long long ro = row_out[rr];
+              const long long ro = ro4[j];
               if (ro >= 0 && n + h2 * 16 + pc * 4 < p.n_valid)
                 *(reinterpret_cast<float4*>(static_cast<float*>(p.out) + ro + n + h2 * 16) + pc) =
-                    *reinterpret_cast<const float4*>(tile + rr * kTilePitch + pc * 16);
+                    *reinterpret_cast<const float4*>(tile + PT_TILE_OFF(rr, pc));
             }
           }
         } else {
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<uint4*>(tile + lane * kTilePitch + i * 16) = make_uint4(
+            *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, i)) = make_uint4(
                 pt::pack_bf16x2(apply_act(f[8 * i], p.act, p.slope), apply_act(f[8 * i + 1], p.act, p.slope)),
                 pt::pack_bf16x2(apply_act(f[8 * i + 2], p.act, p.slope), apply_act(f[8 * i + 3], p.act, p.slope)),
                 pt::pack_bf16x2(apply_act(f[8 * i + 4], p.act, p.slope), apply_act(f[8 * i + 5], p.act, p.slope)),
@@ -540,10 +552,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int rr = pr + 8 * j;
-            const long long ro = row_out[rr];
+            const long long ro = ro4[j];
             if (ro >= 0 && n + pc * 8 < p.n_valid)
               *(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + n) + pc) =
-                  *reinterpret_cast<const uint4*>(tile + rr * kTilePitch + pc * 16);
+                  *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pc));
           }
         }
       }
