@@ -435,10 +435,10 @@ class StackPlanner:
            accumulate across layers); r: pre-norm sum x + style(...) in bf16; LayerNorm statistics are fp32
     memb : bf16 memory rows [B*Mem, 512]; labels int32 [B]."""
 
-    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device, fuse_style=True, fuse_norm=False):
+    def __init__(self, plan: Plan, W: StackWeights, B, N, Mem, labels, device, fuse_style=True, fuse_norm=True):
         self.p, self.W, self.B, self.N, self.Mem = plan, W, B, N, Mem
         # fuse_style: out-proj / FF2 GEMM + style LayerNorm-modulation-SiLU in one kernel (cluster row-norm epilogue)
-        # fuse_norm : style GEMM + residual + LayerNorm in one kernel (correct, but slower than GEMM + LN pass today)
+        # fuse_norm : style GEMM + residual + LayerNorm in one kernel (107 us vs 54 + 59 us unfused at M = 90112)
         self.fuse_style, self.fuse_norm = fuse_style, fuse_norm
         M = B * N
         self.M = M

@@ -288,3 +288,59 @@ def test_wrapper_api_roundtrip(states):
     assert rec.shape == (2, 376, 296)
     qo = vqt.VQ.vq_layer(torch.randn(2, 512, 9).cuda())
     assert qo.quantized.shape == (2, 512, 9) and qo.loss.shape == (2, 9, 4)
+
+
+def _frechet(a, b):
+    """Frechet distance between Gaussians fitted to two feature sets (formula of evaluation/FGD.py:200-257)."""
+    import numpy as np
+    from scipy import linalg
+    mu1, mu2 = a.mean(0), b.mean(0)
+    s1, s2 = np.cov(a, rowvar=False), np.cov(b, rowvar=False)
+    covmean, _ = linalg.sqrtm(s1.dot(s2), disp=False)
+    if not np.isfinite(covmean).all():
+        off = np.eye(s1.shape[0]) * 1e-6
+        covmean = linalg.sqrtm((s1 + off).dot(s2 + off))
+    covmean = covmean.real
+    d = mu1 - mu2
+    return float(d.dot(d) + np.trace(s1) + np.trace(s2) - 2 * np.trace(covmean))
+
+
+def _diversity(poses):
+    """mean pairwise L1 distance between the samples generated for one clip (evaluation/metrics.py:96-110)."""
+    B = poses.shape[0]
+    flat = poses.reshape(B, -1)
+    d = (flat[:, None] - flat[None]).abs().mean(-1)
+    return float(d.sum() / (B * (B - 1)))
+
+
+def test_fgd_and_diversity_unchanged(states, weights):
+    """north_star: 'FGD / diversity on identical inputs must be unchanged'.  The trained FGD feature extractor
+    (experiments/val_models/*.pth) is not available, so features come from a fixed-seed random conv embedding
+    (SURVEY.md 8c caveat 3).  16 samples of one clip from the CUDA predictor vs 16 from the oracle with the same
+    injected noise, and vs a second oracle run with different noise as the yardstick."""
+    import torch.nn.functional as F
+    from probtalk_b200 import engine as E
+    vq, pst, rst = states
+    B, T = 16, 180
+    aud = S.synthetic_audio(1, T, 301).repeat(B, 1, 1)
+    gt = torch.zeros(B, 376, T)
+    mask = torch.zeros(B, 1, T)
+    labels = torch.full((B,), 2)
+    u, gum = noise(8, B, 88, 302)
+    plan = E.PredictorPlan(weights[1], weights[0], B, T)
+    gpu, _ = plan.run(aud.cuda(), gt.cuda(), mask.cuda(), labels.int().cuda(), noise=(u.cuda(), gum.cuda()))
+    gpu = gpu.cpu()
+    ora, _ = O.predictor_infer_on_batch(aud, gt, mask, labels, pst, vq, u, gum)
+    u2, gum2 = noise(8, B, 88, 303)
+    ora2, _ = O.predictor_infer_on_batch(aud, gt, mask, labels, pst, vq, u2, gum2)
+    g = torch.Generator().manual_seed(0)
+    w = torch.randn(32, 376, 15, generator=g) / (376 * 15) ** 0.5
+
+    def feats(p):
+        return torch.tanh(F.conv1d(p, w, stride=5)).permute(0, 2, 1).reshape(-1, 32).double().numpy()
+
+    fd_same = _frechet(feats(gpu), feats(ora))          # CUDA vs oracle, same noise
+    fd_yard = _frechet(feats(ora2), feats(ora))         # oracle vs oracle, different noise
+    assert fd_same <= 1.5 * fd_yard + 1e-3, (fd_same, fd_yard)
+    dv_gpu, dv_ora, dv_ora2 = _diversity(gpu), _diversity(ora), _diversity(ora2)
+    assert abs(dv_gpu - dv_ora) <= max(0.1 * dv_ora, 2 * abs(dv_ora2 - dv_ora)), (dv_gpu, dv_ora, dv_ora2)
