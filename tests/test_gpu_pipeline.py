@@ -296,10 +296,10 @@ def _frechet(a, b):
     from scipy import linalg
     mu1, mu2 = a.mean(0), b.mean(0)
     s1, s2 = np.cov(a, rowvar=False), np.cov(b, rowvar=False)
-    covmean, _ = linalg.sqrtm(s1.dot(s2), disp=False)
+    covmean = np.asarray(linalg.sqrtm(s1.dot(s2)))
     if not np.isfinite(covmean).all():
         off = np.eye(s1.shape[0]) * 1e-6
-        covmean = linalg.sqrtm((s1 + off).dot(s2 + off))
+        covmean = np.asarray(linalg.sqrtm((s1 + off).dot(s2 + off)))
     covmean = covmean.real
     d = mu1 - mu2
     return float(d.dot(d) + np.trace(s1) + np.trace(s2) - 2 * np.trace(covmean))
