@@ -5,15 +5,16 @@
 //     S[128 x Nk]  = Q K^T        tcgen05.mma, Q and K straight from TMA (SWIZZLE_128B, K-major)
 //     P            = softmax(S)   one thread per query row, S read from TMEM, P written to smem as bf16 (K-major)
 //     O[128 x 64]  = P V          tcgen05.mma, V used in place as an MN-major operand (no transpose)
-// Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K/V), warp 1 = MMA issuer, warps 2-5 = softmax /
-// epilogue (TMEM lane = query row).  The S MMA of unit u+1 overlaps the softmax of unit u.
+// Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K/V), warp 1 = MMA issuer, warps 2-5 = softmax (TMEM lane =
+// query row), warps 6-9 = output (O read-out, 1/sum scaling, stores).  The S MMA and softmax of unit u+1 overlap the
+// P V MMA and the output stage of unit u.
 #include <cuda.h>
 #include "pt_common.cuh"
 #include "pt_host.h"
 
 namespace {
 
-constexpr int kThreadsTc = 6 * 32;
+constexpr int kThreadsTc = 10 * 32;   // TMA, MMA, 4 softmax warps, 4 output warps
 constexpr int kQRows = 128;
 constexpr uint32_t kQBytes = kQRows * 128;          // 16 KB
 constexpr uint32_t kAtomBytes = kQRows * 128;       // one [128 x 64] bf16 swizzle atom of P
@@ -25,6 +26,7 @@ struct AttnTcArgs {
   int B, m_tiles;                  // m_tiles = ceil(Nq / 128)
   int tmem_cols, o_col;            // TMEM allocation (power of two) and the column where O starts
   int nstage;                      // Q/K/V smem stages (2 = prefetch the next unit)
+  int s_bufs;                      // S accumulators in TMEM (2 = the next unit's Q K^T overlaps this unit's softmax)
   float scale_log2e;
 };
 
@@ -32,6 +34,27 @@ __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+__device__ __forceinline__ void fma2(float& a0, float& a1, float x0, float x1, float y0, float y1, float z0, float z1) {
+  unsigned long long x, y, z, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(x) : "f"(x0), "f"(x1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(y) : "f"(y0), "f"(y1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(z) : "f"(z0), "f"(z1));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(x), "l"(y), "l"(z));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(d));
+}
+__device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {
+  unsigned long long a, b, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(d));
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
 }
 
 // smem matrix descriptor, MN-major operand, SWIZZLE_128B: 64 MN-elements (128 B) per row, rows = K index;
@@ -56,14 +79,16 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const uint32_t stage_bytes = kQBytes + 2 * kv_pad;
   const int p_atoms = (a.NKP + 63) / 64;
   uint8_t* p_smem = smem + (size_t)a.nstage * stage_bytes;
-  __shared__ uint64_t bars[9];
+  __shared__ uint64_t bars[13];
+  __shared__ float sums_s[2][kQRows];          // softmax row sums, handed from the softmax warps to the output warps
   uint64_t* qkv_full = bars;        // [2]
   uint64_t* qkv_empty = bars + 2;   // [2]
-  uint64_t* s_full = bars + 4;
-  uint64_t* s_free = bars + 5;
-  uint64_t* p_full = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint64_t* o_free = bars + 8;
+  uint64_t* s_full = bars + 4;      // [2]  (S is double-buffered in TMEM when it fits)
+  uint64_t* s_free = bars + 6;      // [2]
+  uint64_t* p_full = bars + 8;
+  uint64_t* o_full = bars + 9;
+  uint64_t* o_free = bars + 10;
+  uint64_t* sums_full = bars + 11;  // [2]
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -72,8 +97,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   if (warp == 0 && lane == 0) {
     pt::tma_prefetch_desc(&tmap_q); pt::tma_prefetch_desc(&tmap_k); pt::tma_prefetch_desc(&tmap_v);
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&qkv_full[i], 1); pt::mbar_init(&qkv_empty[i], 1); }
-    pt::mbar_init(s_full, 1); pt::mbar_init(s_free, 4); pt::mbar_init(p_full, 4);
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&s_full[i], 1); pt::mbar_init(&s_free[i], 4); }
+    pt::mbar_init(p_full, 4);
     pt::mbar_init(o_full, 1); pt::mbar_init(o_free, 4);
+    pt::mbar_init(&sums_full[0], 4); pt::mbar_init(&sums_full[1], 4);
     pt::fence_mbar_init();
   }
   if (warp == 1) { pt::tmem_alloc(&tmem_slot, (uint32_t)a.tmem_cols); pt::tmem_relinquish(); }
@@ -82,6 +109,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   pt::tc_fence_after();
   const uint32_t tmem = tmem_slot;
   const uint32_t tmem_s = tmem, tmem_o = tmem + (uint32_t)a.o_col;
+  const bool dbl = (a.s_bufs == 2);
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -105,19 +133,32 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     if (lane == 0) {
       const uint32_t idesc_s = pt::umma_idesc_bf16(kQRows, (uint32_t)a.NKP);
       const uint32_t idesc_o = pt::umma_idesc_bf16(kQRows, 64) | (1u << 16);       // B operand (V) is MN-major
-      int it = 0;
-      for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
+      // S(u) = Q K^T into S buffer (u & 1 when double-buffered); issued one unit AHEAD of the P V MMA so that it runs
+      // while the softmax warps are still busy with the previous unit
+      auto issue_s = [&](int it) {
         const int st = (a.nstage == 2) ? (it & 1) : 0;
-        const uint32_t ph = (uint32_t)((a.nstage == 2) ? (it >> 1) : it) & 1u, up = (uint32_t)it & 1u;
+        const uint32_t ph = (uint32_t)((a.nstage == 2) ? (it >> 1) : it) & 1u;
+        const int sb = dbl ? (it & 1) : 0;
+        const uint32_t sph = (uint32_t)(dbl ? (it >> 1) : it) & 1u;
         const uint32_t sq = pt::smem_u32(smem + (size_t)st * stage_bytes);
-        const uint32_t sk = sq + kQBytes, sv = sk + kv_pad;
+        const uint32_t sk = sq + kQBytes;
         pt::mbar_wait(&qkv_full[st], ph);
-        pt::mbar_wait(s_free, up ^ 1);                   // softmax of the previous unit has read S
+        pt::mbar_wait(&s_free[sb], sph ^ 1);             // the softmax that last used this S buffer has read it
         pt::tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          pt::umma_bf16(tmem_s, pt::umma_desc_sw128(sq + k * 32), pt::umma_desc_sw128(sk + k * 32), idesc_s, k ? 1u : 0u);
-        pt::umma_commit(s_full);
+          pt::umma_bf16(tmem_s + sb * a.NKP, pt::umma_desc_sw128(sq + k * 32), pt::umma_desc_sw128(sk + k * 32), idesc_s, k ? 1u : 0u);
+        pt::umma_commit(&s_full[sb]);
+      };
+      const bool ahead = dbl && a.nstage == 2;
+      int it = 0;
+      if (ahead && (int)blockIdx.x < n_units) issue_s(0);
+      for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
+        const int st = (a.nstage == 2) ? (it & 1) : 0;
+        const uint32_t up = (uint32_t)it & 1u;
+        if (ahead) { if (u + (int)gridDim.x < n_units) issue_s(it + 1); }
+        else issue_s(it);
+        const uint32_t sv = pt::smem_u32(smem + (size_t)st * stage_bytes) + kQBytes + kv_pad;
         pt::mbar_wait(p_full, up);                       // P (bf16) is in smem
         pt::mbar_wait(o_free, up ^ 1);                   // the previous O has been read out of TMEM
         pt::tc_fence_after();
@@ -130,41 +171,55 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         pt::umma_commit(&qkv_empty[st]);                 // Q/K/V stage (and P) consumed
       }
     }
-  } else {
-    // ------------------------------------------------------------ softmax + epilogue (thread = query row)
+  } else if (warp < 6) {
+    // ------------------------------------------------------------ softmax (thread = query row)
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     int it = 0;
     for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
       const uint32_t up = (uint32_t)it & 1u;
-      const int mt = u % a.m_tiles, bh = u / a.m_tiles;
-      const int h = bh % a.heads, b = bh / a.heads;
-      pt::mbar_wait(s_full, up);
+      const int sb = dbl ? (it & 1) : 0;
+      const uint32_t sph = (uint32_t)(dbl ? (it >> 1) : it) & 1u;
+      const uint32_t tmem_sb = tmem_s + sb * a.NKP;
+      pt::mbar_wait(&s_full[sb], sph);
       pt::tc_fence_after();
-      // pass 1: row maximum
+      // pass 1: row maximum (only the last 32-column chunk can hold keys beyond Nk)
       float mx = -INFINITY;
       for (int c0 = 0; c0 < a.NKP; c0 += 32) {
         uint32_t v[32];
-        pt::tmem_ld32(tmem_s + lane_off + c0, v);
+        pt::tmem_ld32(tmem_sb + lane_off + c0, v);
         pt::tmem_ld_wait();
+        if (c0 + 32 <= a.Nk) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (c0 + i < a.Nk) mx = fmaxf(mx, __uint_as_float(v[i]));
+          for (int i = 0; i < 32; i += 2) mx = max3(mx, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c0 + i < a.Nk) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
       }
-      // pass 2: P = exp2((s - max) * scale * log2e) as bf16 into the K-major swizzled A tile; row sum in fp32
-      float sum = 0.f;
-      const float mxs = mx * a.scale_log2e;
+      // the P tile is single-buffered: the P V MMA of the previous unit must have finished reading it
+      if (it > 0) pt::mbar_wait(o_full, up ^ 1);
+      // pass 2: P = exp2(s * scale*log2e - max * scale*log2e) as bf16 into the K-major swizzled A tile; fp32 row sum
+      float sum0 = 0.f, sum1 = 0.f;
+      const float nmxs = -mx * a.scale_log2e, sc = a.scale_log2e;
       for (int c0 = 0; c0 < a.NKP; c0 += 32) {
         uint32_t v[32];
-        pt::tmem_ld32(tmem_s + lane_off + c0, v);
+        pt::tmem_ld32(tmem_sb + lane_off + c0, v);
         pt::tmem_ld_wait();
         uint32_t pk[16];
+        const bool full = (c0 + 32 <= a.Nk);
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const float p0 = (c0 + 2 * i < a.Nk) ? ex2(fmaf(__uint_as_float(v[2 * i]), a.scale_log2e, -mxs)) : 0.f;
-          const float p1 = (c0 + 2 * i + 1 < a.Nk) ? ex2(fmaf(__uint_as_float(v[2 * i + 1]), a.scale_log2e, -mxs)) : 0.f;
-          sum += p0 + p1;
+          float t0, t1;
+          fma2(t0, t1, __uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), sc, sc, nmxs, nmxs);
+          float p0 = ex2(t0), p1 = ex2(t1);
+          if (!full) {
+            if (c0 + 2 * i >= a.Nk) p0 = 0.f;
+            if (c0 + 2 * i + 1 >= a.Nk) p1 = 0.f;
+          }
+          add2(sum0, sum1, p0, p1);
           pk[i] = pt::pack_bf16x2(p0, p1);
         }
         uint8_t* atom = p_smem + (size_t)(c0 >> 6) * kAtomBytes;
@@ -174,15 +229,27 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           *reinterpret_cast<uint4*>(atom + pt::sw128_offset(row, chunk0 + i)) =
               make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
       }
-      // keys NKP .. p_atoms*64 of the last atom are never read by the PV MMA (it stops at NKP)
+      const float sum = sum0 + sum1;
+      sums_s[up][row] = sum;
       pt::tc_fence_before();
       pt::fence_async_smem();                            // P stores -> visible to the tensor-core proxy
       __syncwarp();
-      if (lane == 0) { pt::mbar_arrive(s_free); pt::mbar_arrive(p_full); }
-      // O = P V
+      if (lane == 0) { pt::mbar_arrive(&s_free[sb]); pt::mbar_arrive(p_full); pt::mbar_arrive(&sums_full[up]); }
+    }
+  } else {
+    // ------------------------------------------------------------ output: O = P V read-out, 1/sum, stores
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    int it = 0;
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
+      const uint32_t up = (uint32_t)it & 1u;
+      const int mt = u % a.m_tiles, bh = u / a.m_tiles;
+      const int h = bh % a.heads, b = bh / a.heads;
+      pt::mbar_wait(&sums_full[up], (uint32_t)(it >> 1) & 1u);
       pt::mbar_wait(o_full, up);
       pt::tc_fence_after();
-      const float inv = 1.f / sum;
+      const float inv = 1.f / sums_s[up][row];
       const int qrow = mt * kQRows + row;
       uint32_t o0[32], o1[32];
       pt::tmem_ld32(tmem_o + lane_off, o0);
@@ -259,9 +326,10 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
   const uint32_t kv_pad = ((uint32_t)a.NKP * 128u + 1023u) & ~1023u;
   const size_t stage = kQBytes + 2 * (size_t)kv_pad, ptile = (size_t)((a.NKP + 63) / 64) * kAtomBytes;
   // TMEM: S (NKP columns) + O (64 columns), rounded to a power of two; smaller allocations let several CTAs share an SM
-  a.o_col = a.NKP;
+  a.s_bufs = (2 * a.NKP + 64 <= 512) ? 2 : 1;
+  a.o_col = a.s_bufs * a.NKP;
   a.tmem_cols = 32;
-  while (a.tmem_cols < a.NKP + 64) a.tmem_cols *= 2;
+  while (a.tmem_cols < a.o_col + 64) a.tmem_cols *= 2;
   const int by_tmem = 512 / a.tmem_cols;
   // the unit chain (MMA -> softmax -> MMA -> store) is latency bound, so co-resident CTAs matter more than prefetch depth
   const size_t sm_smem = 227 * 1024;
