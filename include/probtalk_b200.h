@@ -94,6 +94,8 @@ typedef struct pt_gemm_desc {
   const float* norm_b;    /* fp32 [n_classes, 512] */
   const int* labels;      /* int32 per sample or NULL */
   int label_rows;
+  int norm_classes;       /* rows of norm_a / norm_b that labels may select: 1..4 when labels is not NULL (the tables are
+                           * staged on chip; labels are clamped to the range) */
 } pt_gemm_desc;
 
 int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);

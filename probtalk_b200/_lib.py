@@ -30,6 +30,7 @@ class GemmDesc(C.Structure):
         ("slope", C.c_float),
         ("row_norm", C.c_int), ("norm_a", C.c_void_p), ("norm_b", C.c_void_p), ("labels", C.c_void_p),
         ("label_rows", C.c_int),
+        ("norm_classes", C.c_int),
     ]
 
 

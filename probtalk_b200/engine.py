@@ -191,6 +191,7 @@ class Plan:
         d.row_norm, d.label_rows = row_norm, label_rows
         d.norm_a = norm_a.data_ptr() if norm_a is not None else None
         d.norm_b = norm_b.data_ptr() if norm_b is not None else None
+        d.norm_classes = (norm_a.numel() // 512) if norm_a is not None else 0
         d.labels = labels.data_ptr() if labels is not None else None
         self.keep += [a_t, w, out_t, residual, d, norm_a, norm_b, labels]
         # algorithmic FLOPs: real output rows x real output channels x real input channels (no padding / halo credit)

@@ -59,16 +59,26 @@ def _device(args):
 
 
 class _Timer:
+    """The reference brackets every infer_* call with torch.cuda.synchronize() + time.time() and returns the seconds
+    (predictor.py:423-443, refiner.py:541-554).  ``blocking=True`` keeps that contract (CUDA events instead of
+    wall-clock); ``blocking=False`` (wrapper attribute ``sync_timing = False``) returns 0.0 seconds and never
+    synchronises, so a caller can overlap copies of the next batch with this batch's kernels."""
+
+    def __init__(self, blocking=True):
+        self.blocking, self.seconds = blocking, 0.0
+
     def __enter__(self):
-        self.e0, self.e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        self.e0.record()
+        if self.blocking:
+            self.e0, self.e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            self.e0.record()
         return self
 
     def __exit__(self, *a):
-        self.e1.record()
-        torch.cuda.synchronize()
-        self.seconds = self.e0.elapsed_time(self.e1) * 1e-3
+        if self.blocking:
+            self.e1.record()
+            torch.cuda.synchronize()
+            self.seconds = self.e0.elapsed_time(self.e1) * 1e-3
 
 
 class PQLayer(M.ProductQuantizationParams):
@@ -181,6 +191,7 @@ class _WrapperBase:
         self.num_classes = _n_classes(config)
         self.global_step = 0
         self.generator_optimizer = None
+        self.sync_timing = True       # False: infer_* calls do not synchronise and report 0.0 seconds
 
     def _make_vq(self, in_dim):
         m = self.config.Model
@@ -224,7 +235,7 @@ class s2g_body_vqt(_WrapperBase):
     def infer_on_audio(self, gt_poses, aud=None, text=None, id=None, B=1, **kw):
         """encode -> product-quantise -> decode (vq_teacher.py:255-275)."""
         assert self.args.infer, "train mode"
-        with _Timer() as t:
+        with _Timer(self.sync_timing) as t:
             pred = self.VQ(gt_poses=gt_poses)
         return pred, t.seconds
 
@@ -278,7 +289,7 @@ class s2g_body_predictor(_WrapperBase):
             aud = aud.repeat(B, 1, 1)                         # predictor.py:415
         T = aud.shape[2]
         plan = self._plan(B, T)
-        with _Timer() as t:
+        with _Timer(self.sync_timing) as t:
             poses, codes = plan.run(aud, gt_poses.to(dev, torch.float32), mask.to(dev, torch.float32),
                                     self._labels(id, B), noise=noise, generator=self.noise_generator)
         return poses.clone(), codes.to(torch.int32).clone(), t.seconds
@@ -330,7 +341,7 @@ class s2g_body_refiner(_WrapperBase):
             aud = aud.repeat(B, 1, 1)
         T = aud.shape[2]
         plan = self._plan(B, T, pred_poses.shape[2])
-        with _Timer() as t:
+        with _Timer(self.sync_timing) as t:
             out = plan.run(aud, gt_poses.to(dev, torch.float32), mask.to(dev, torch.float32),
                            pred_poses.to(dev, torch.float32), self._labels(id, B))
         return out.clone(), t.seconds

@@ -121,5 +121,6 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
     d.rss, d.rrs = rss, rrs
     d.act, d.slope = act, slope
     d.row_norm, d.norm_a, d.norm_b, d.labels, d.label_rows = row_norm, _ptr(norm_a), _ptr(norm_b), _ptr(labels), label_rows
+    d.norm_classes = (norm_a.numel() // 512) if norm_a is not None else 0
     check(_lib.lib().pt_gemm_bf16(C.byref(d), _stream()), "pt_gemm_bf16")
     return out

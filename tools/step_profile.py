@@ -30,8 +30,8 @@ for pl in plans:
         key = fn.__name__
         if key == "pt_gemm_bf16":
             d = args[0]._obj
-            key = "gemm M=%d N=%d K=%d taps=%d s=%d out=%s res=%s act=%d ocs1=%d" % (d.M, d.n_valid, d.taps * d.C, d.taps, d.s, "f32" if d.out_f32 else "bf16",
-                                                                            ("f32" if d.res_f32 else "bf16") if d.residual else "-", d.act, int(d.ocs == 1))
+            key = "gemm M=%d N=%d K=%d taps=%d s=%d out=%s res=%s act=%d ocs1=%d rn=%d" % (d.M, d.n_valid, d.taps * d.C, d.taps, d.s, "f32" if d.out_f32 else "bf16",
+                                                                            ("f32" if d.res_f32 else "bf16") if d.residual else "-", d.act, int(d.ocs == 1), d.row_norm)
         elif key == "pt_attention":
             key = "attention Nq=%d Nk=%d" % (args[11], args[12])
         recs.append((key, e0, e1, flops))
