@@ -5,10 +5,14 @@
 //     S[128 x Nk]  = Q K^T        tcgen05.mma, Q and K straight from TMA (SWIZZLE_128B, K-major)
 //     P            = softmax(S)   one thread per query row, S read from TMEM, P written to smem as bf16 (K-major)
 //     O[128 x 64]  = P V          tcgen05.mma, V used in place as an MN-major operand (no transpose)
-// Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K/V), warp 1 = MMA issuer, warps 2-5 = softmax (TMEM lane =
-// query row), warps 6-9 = output (O read-out, 1/sum scaling, stores).  The S MMA and softmax of unit u+1 overlap the
-// P V MMA and the output stage of unit u.
+// Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K and V, separate barriers), warp 1 = MMA issuer, warps 2-5 =
+// softmax (TMEM lane = query row), warps 6-9 = output (O read-out, 1/sum scaling, stores).
+// The unit chain (load -> Q K^T -> softmax -> P V -> store) is latency bound, so the stages are decoupled as far as the
+// buffers allow: the issuer thread POLLS two independent queues (next Q K^T, next P V) instead of blocking on either,
+// Q/K slots are released as soon as their Q K^T has run (not after P V), and V has its own full / empty barriers.  With
+// two S accumulators in TMEM the loads and the Q K^T of unit u+2 are in flight while unit u is still in its softmax.
 #include <cuda.h>
+#include <stdlib.h>
 #include "pt_common.cuh"
 #include "pt_host.h"
 
@@ -26,6 +30,10 @@ struct AttnTcArgs {
   int B, m_tiles;                  // m_tiles = ceil(Nq / 128)
   int tmem_cols, o_col;            // TMEM allocation (power of two) and the column where O starts
   int nstage;                      // Q/K/V smem stages (2 = prefetch the next unit)
+  int kv_rows;                     // rows of the K / V TMA boxes (NKP, or Nk rounded up to 8: see pt_attention_tc)
+  int q_region;                    // bytes reserved for Q in a stage (q_box rows rounded up to 1 KB; the M = 128 MMA may
+                                   // read on into K, which only produces score rows that are never stored)
+  int q_box;                       // rows of the Q TMA box (Nq rounded up to 8 when one tile covers all queries)
   int s_bufs;                      // S accumulators in TMEM (2 = the next unit's Q K^T overlaps this unit's softmax)
   float scale_log2e;
 };
@@ -74,29 +82,40 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     const __grid_constant__ CUtensorMap tmap_v, const AttnTcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const uint32_t kv_bytes = (uint32_t)a.NKP * 128u;
+  const uint32_t kv_bytes = (uint32_t)a.kv_rows * 128u;
   const uint32_t kv_pad = (kv_bytes + 1023u) & ~1023u;
-  const uint32_t stage_bytes = kQBytes + 2 * kv_pad;
+  const uint32_t q_region = (uint32_t)a.q_region;
+  const uint32_t stage_bytes = q_region + 2 * kv_pad;
   const int p_atoms = (a.NKP + 63) / 64;
   uint8_t* p_smem = smem + (size_t)a.nstage * stage_bytes;
-  __shared__ uint64_t bars[13];
+  __shared__ uint64_t bars[17];
   __shared__ float sums_s[2][kQRows];          // softmax row sums, handed from the softmax warps to the output warps
-  uint64_t* qkv_full = bars;        // [2]
-  uint64_t* qkv_empty = bars + 2;   // [2]
+  uint64_t* qk_full = bars;         // [2]  Q and K of a unit have landed
+  uint64_t* qk_empty = bars + 2;    // [2]  ... and its Q K^T has finished reading them
   uint64_t* s_full = bars + 4;      // [2]  (S is double-buffered in TMEM when it fits)
   uint64_t* s_free = bars + 6;      // [2]
   uint64_t* p_full = bars + 8;
   uint64_t* o_full = bars + 9;
   uint64_t* o_free = bars + 10;
   uint64_t* sums_full = bars + 11;  // [2]
+  uint64_t* v_full = bars + 13;     // [2]  V of a unit has landed
+  uint64_t* v_empty = bars + 15;    // [2]  ... and its P V has finished reading it
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_units = a.B * a.heads * a.m_tiles;
 
+  {
+    // Operand rows that no TMA box ever writes (keys beyond the box, see kv_rows) are read by the MMAs; they must hold
+    // finite numbers (they meet P = 0 or masked score columns), so the whole buffer starts as zeros.
+    const uint32_t total = (uint32_t)a.nstage * stage_bytes + (uint32_t)p_atoms * kAtomBytes;
+    for (uint32_t i = threadIdx.x * 16u; i < total; i += kThreadsTc * 16u) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+    pt::fence_async_smem();
+  }
   if (warp == 0 && lane == 0) {
     pt::tma_prefetch_desc(&tmap_q); pt::tma_prefetch_desc(&tmap_k); pt::tma_prefetch_desc(&tmap_v);
-    for (int i = 0; i < 2; ++i) { pt::mbar_init(&qkv_full[i], 1); pt::mbar_init(&qkv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&qk_full[i], 1); pt::mbar_init(&qk_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&v_full[i], 1); pt::mbar_init(&v_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&s_full[i], 1); pt::mbar_init(&s_free[i], 4); }
     pt::mbar_init(p_full, 4);
     pt::mbar_init(o_full, 1); pt::mbar_init(o_free, 4);
@@ -120,12 +139,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const uint32_t ph = (uint32_t)((a.nstage == 2) ? (it >> 1) : it) & 1u;
         const int mt = u % a.m_tiles, bh = u / a.m_tiles;
         const int h = bh % a.heads, b = bh / a.heads;
-        pt::mbar_wait(&qkv_empty[st], ph ^ 1);
         uint8_t* sq = smem + (size_t)st * stage_bytes;
-        pt::mbar_expect_tx(&qkv_full[st], kQBytes + 2 * kv_bytes);
-        pt::tma_load_2d(sq, &tmap_q, &qkv_full[st], h * 64, b * a.Nq + mt * kQRows);
-        pt::tma_load_2d(sq + kQBytes, &tmap_k, &qkv_full[st], h * 64, b * a.Nk);
-        pt::tma_load_2d(sq + kQBytes + kv_pad, &tmap_v, &qkv_full[st], h * 64, b * a.Nk);
+        pt::mbar_wait(&qk_empty[st], ph ^ 1);
+        pt::mbar_expect_tx(&qk_full[st], (uint32_t)a.q_box * 128u + kv_bytes);
+        pt::tma_load_2d(sq, &tmap_q, &qk_full[st], h * 64, b * a.Nq + mt * kQRows);
+        pt::tma_load_2d(sq + q_region, &tmap_k, &qk_full[st], h * 64, b * a.Nk);
+        pt::mbar_wait(&v_empty[st], ph ^ 1);
+        pt::mbar_expect_tx(&v_full[st], kv_bytes);
+        pt::tma_load_2d(sq + q_region + kv_pad, &tmap_v, &v_full[st], h * 64, b * a.Nk);
       }
     }
   } else if (warp == 1) {
@@ -133,42 +154,48 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     if (lane == 0) {
       const uint32_t idesc_s = pt::umma_idesc_bf16(kQRows, (uint32_t)a.NKP);
       const uint32_t idesc_o = pt::umma_idesc_bf16(kQRows, 64) | (1u << 16);       // B operand (V) is MN-major
-      // S(u) = Q K^T into S buffer (u & 1 when double-buffered); issued one unit AHEAD of the P V MMA so that it runs
-      // while the softmax warps are still busy with the previous unit
-      auto issue_s = [&](int it) {
-        const int st = (a.nstage == 2) ? (it & 1) : 0;
-        const uint32_t ph = (uint32_t)((a.nstage == 2) ? (it >> 1) : it) & 1u;
-        const int sb = dbl ? (it & 1) : 0;
-        const uint32_t sph = (uint32_t)(dbl ? (it >> 1) : it) & 1u;
-        const uint32_t sq = pt::smem_u32(smem + (size_t)st * stage_bytes);
-        const uint32_t sk = sq + kQBytes;
-        pt::mbar_wait(&qkv_full[st], ph);
-        pt::mbar_wait(&s_free[sb], sph ^ 1);             // the softmax that last used this S buffer has read it
-        pt::tc_fence_after();
+      // Two queues, polled without blocking: S(i) = Q K^T of this CTA's i-th unit, O(j) = P V of its j-th unit.
+      // S runs ahead of P V as far as the S accumulators and the Q/K slots allow (the barriers say when).
+      const int n_my = (n_units > (int)blockIdx.x) ? (n_units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+      const int ksteps = a.NKP / 16;
+      const uint32_t sp = pt::smem_u32(p_smem);
+      int is = 0, ip = 0;
+      uint32_t spins = 0;
+      while (ip < n_my) {
+        bool progressed = false;
+        // P V first: the single P tile and O accumulator gate the next unit's softmax, Q K^T only has to stay ahead
+        if (ip < is) {
+          const int st = ip % a.nstage;
+          const uint32_t ph = (uint32_t)(ip / a.nstage) & 1u, up = (uint32_t)ip & 1u;
+          // P (bf16) is in smem, the previous O has been read out of TMEM, V has landed
+          if (pt::mbar_test_wait(p_full, up) && pt::mbar_test_wait(o_free, up ^ 1) && pt::mbar_test_wait(&v_full[st], ph)) {
+            const uint32_t sv = pt::smem_u32(smem + (size_t)st * stage_bytes) + q_region + kv_pad;
+            pt::tc_fence_after();
+            for (int j = 0; j < ksteps; ++j)
+              pt::umma_bf16(tmem_o, pt::umma_desc_sw128(sp + (j >> 2) * kAtomBytes + (j & 3) * 32),
+                            umma_desc_sw128_mn(sv + j * 2048), idesc_o, j ? 1u : 0u);
+            pt::umma_commit(o_full);
+            pt::umma_commit(&v_empty[st]);
+            ++ip; progressed = true;
+          }
+        }
+        if (is < n_my) {
+          const int st = is % a.nstage, sb = is % a.s_bufs;
+          const uint32_t ph = (uint32_t)(is / a.nstage) & 1u, sph = (uint32_t)(is / a.s_bufs) & 1u;
+          if (pt::mbar_test_wait(&qk_full[st], ph) && pt::mbar_test_wait(&s_free[sb], sph ^ 1)) {
+            const uint32_t sq = pt::smem_u32(smem + (size_t)st * stage_bytes);
+            const uint32_t sk = sq + q_region;
+            pt::tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          pt::umma_bf16(tmem_s + sb * a.NKP, pt::umma_desc_sw128(sq + k * 32), pt::umma_desc_sw128(sk + k * 32), idesc_s, k ? 1u : 0u);
-        pt::umma_commit(&s_full[sb]);
-      };
-      const bool ahead = dbl && a.nstage == 2;
-      int it = 0;
-      if (ahead && (int)blockIdx.x < n_units) issue_s(0);
-      for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++it) {
-        const int st = (a.nstage == 2) ? (it & 1) : 0;
-        const uint32_t up = (uint32_t)it & 1u;
-        if (ahead) { if (u + (int)gridDim.x < n_units) issue_s(it + 1); }
-        else issue_s(it);
-        const uint32_t sv = pt::smem_u32(smem + (size_t)st * stage_bytes) + kQBytes + kv_pad;
-        pt::mbar_wait(p_full, up);                       // P (bf16) is in smem
-        pt::mbar_wait(o_free, up ^ 1);                   // the previous O has been read out of TMEM
-        pt::tc_fence_after();
-        const uint32_t sp = pt::smem_u32(p_smem);
-        const int ksteps = a.NKP / 16;
-        for (int j = 0; j < ksteps; ++j)
-          pt::umma_bf16(tmem_o, pt::umma_desc_sw128(sp + (j >> 2) * kAtomBytes + (j & 3) * 32),
-                        umma_desc_sw128_mn(sv + j * 2048), idesc_o, j ? 1u : 0u);
-        pt::umma_commit(o_full);
-        pt::umma_commit(&qkv_empty[st]);                 // Q/K/V stage (and P) consumed
+            for (int k = 0; k < 4; ++k)
+              pt::umma_bf16(tmem_s + sb * a.NKP, pt::umma_desc_sw128(sq + k * 32), pt::umma_desc_sw128(sk + k * 32), idesc_s, k ? 1u : 0u);
+            pt::umma_commit(&s_full[sb]);
+            pt::umma_commit(&qk_empty[st]);              // Q and K of this slot may be overwritten once S is complete
+            ++is; progressed = true;
+          }
+        }
+        if (progressed) spins = 0;
+        else { __nanosleep(40); if (++spins > PT_SPIN_LIMIT) __trap(); }   // yield issue slots to the softmax warps
       }
     }
   } else if (warp < 6) {
@@ -184,6 +211,49 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const uint32_t tmem_sb = tmem_s + sb * a.NKP;
       pt::mbar_wait(&s_full[sb], sph);
       pt::tc_fence_after();
+      // a warp whose 32 rows all lie beyond the last query of this tile (Nq = 88: rows 96..127) only keeps the barrier
+      // protocol going; its P rows stay stale, which is harmless because every O row depends on its own P row only
+      const int rows_valid = min(kQRows, a.Nq - (u % a.m_tiles) * kQRows);
+      if (q * 32 >= rows_valid) {
+        if (it > 0) pt::mbar_wait(o_full, up ^ 1);
+        sums_s[up][row] = 1.f;
+        __syncwarp();
+        if (lane == 0) { pt::mbar_arrive(&s_free[sb]); pt::mbar_arrive(p_full); pt::mbar_arrive(&sums_full[up]); }
+        continue;
+      }
+      if (a.NKP == 32) {
+        // short key sets (cross attention over the 22 memory tokens): one TMEM read, scores stay in registers
+        uint32_t v[32];
+        pt::tmem_ld32(tmem_sb + lane_off, v);
+        pt::tmem_ld_wait();
+        float mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (i < a.Nk) mx = fmaxf(mx, __uint_as_float(v[i]));
+        if (it > 0) pt::mbar_wait(o_full, up ^ 1);
+        float sum0 = 0.f, sum1 = 0.f;
+        const float nmxs = -mx * a.scale_log2e, sc = a.scale_log2e;
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float t0, t1;
+          fma2(t0, t1, __uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), sc, sc, nmxs, nmxs);
+          float p0 = ex2(t0), p1 = ex2(t1);
+          if (2 * i >= a.Nk) p0 = 0.f;
+          if (2 * i + 1 >= a.Nk) p1 = 0.f;
+          add2(sum0, sum1, p0, p1);
+          pk[i] = pt::pack_bf16x2(p0, p1);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          *reinterpret_cast<uint4*>(p_smem + pt::sw128_offset(row, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        sums_s[up][row] = sum0 + sum1;
+        pt::tc_fence_before();
+        pt::fence_async_smem();
+        __syncwarp();
+        if (lane == 0) { pt::mbar_arrive(&s_free[sb]); pt::mbar_arrive(p_full); pt::mbar_arrive(&sums_full[up]); }
+        continue;
+      }
       // pass 1: row maximum (only the last 32-column chunk can hold keys beyond Nk)
       float mx = -INFINITY;
       for (int c0 = 0; c0 < a.NKP; c0 += 32) {
@@ -320,27 +390,40 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
   if ((out_stride & 7) || (reinterpret_cast<uintptr_t>(out) & 15))
     return pt::fail("pt_attention: out must be 16-byte aligned with a row stride multiple of 8 elements");
   CUtensorMap tq, tk, tv;
-  if (make_map(&tq, q, (long long)B * Nq, (long long)heads * 64, q_stride, kQRows)) return 1;
-  if (make_map(&tk, k, (long long)B * Nk, (long long)heads * 64, k_stride, a.NKP)) return 1;
-  if (make_map(&tv, v, (long long)B * Nk, (long long)heads * 64, v_stride, a.NKP)) return 1;
-  const uint32_t kv_pad = ((uint32_t)a.NKP * 128u + 1023u) & ~1023u;
-  const size_t stage = kQBytes + 2 * (size_t)kv_pad, ptile = (size_t)((a.NKP + 63) / 64) * kAtomBytes;
-  // TMEM: S (NKP columns) + O (64 columns), rounded to a power of two; smaller allocations let several CTAs share an SM
-  a.s_bufs = (2 * a.NKP + 64 <= 512) ? 2 : 1;
-  a.o_col = a.s_bufs * a.NKP;
-  a.tmem_cols = 32;
-  while (a.tmem_cols < a.o_col + 64) a.tmem_cols *= 2;
-  const int by_tmem = 512 / a.tmem_cols;
-  // the unit chain (MMA -> softmax -> MMA -> store) is latency bound, so co-resident CTAs matter more than prefetch depth
-  const size_t sm_smem = 227 * 1024;
-  int per_sm = 1;
-  a.nstage = 2;
-  for (int want = (by_tmem < 2 ? by_tmem : 2); want >= 1; --want) {
-    if ((1024 + 2 * stage + ptile + 1024) * want <= sm_smem) { per_sm = want; a.nstage = 2; break; }
-    if ((1024 + stage + ptile + 1024) * want <= sm_smem) { per_sm = want; a.nstage = 1; break; }
+  a.q_box = (a.m_tiles == 1) ? ((Nq + 7) & ~7) : kQRows;
+  if (make_map(&tq, q, (long long)B * Nq, (long long)heads * 64, q_stride, a.q_box)) return 1;
+  // Configurations in order of preference.  The unit chain (load -> MMA -> softmax -> MMA -> store) is latency bound, so
+  // two co-resident CTAs per SM (two softmax warp groups) beat deeper buffering inside one CTA.
+  //   kv_rows: the K / V boxes carry NKP rows, or only Nk rounded up to 8 when that is what lets a second CTA fit.  In
+  //   the short-box layout the K / V regions are kv_rows * 128 bytes apart and the MMAs (which always read NKP rows)
+  //   run up to 1 KB into the neighbouring region: for K those are masked score columns, for V they meet P = 0, and the
+  //   neighbour holds finite bf16 data (V, Q or probabilities; zeros at start), so the products vanish.
+  const size_t sm_smem = 227 * 1024, ptile = (size_t)((a.NKP + 63) / 64) * kAtomBytes;
+  const int kv8 = (Nk + 7) & ~7;
+  a.q_region = (a.q_box * 128 + 1023) & ~1023;
+  struct Cand { int per_sm, nstage, s_bufs, kv_rows; };
+  const Cand cands[] = {{2, 2, 2, a.NKP}, {2, 2, 1, a.NKP}, {2, 1, 2, a.NKP}, {2, 1, 1, a.NKP}, {2, 1, 1, kv8},
+                        {1, 2, 2, a.NKP}, {1, 2, 1, a.NKP}, {1, 1, 1, a.NKP}};
+  int per_sm = 0;
+  size_t stage = 0;
+  for (const Cand& c : cands) {
+    const int cols = c.s_bufs * a.NKP + 64;
+    int tc = 32;
+    while (tc < cols) tc *= 2;
+    if (tc > 512 || tc * c.per_sm > 512) continue;
+    if (c.kv_rows != a.NKP && (a.NKP - c.kv_rows) * 128 > 1024) continue;
+    const size_t kvp = ((size_t)c.kv_rows * 128 + 1023) & ~(size_t)1023;
+    const size_t stg = (size_t)a.q_region + 2 * kvp;
+    // per CTA: 1 KB alignment slack + stages + P tile + ~1.3 KB static + 1 KB reserved by the driver
+    if ((1024 + c.nstage * stg + ptile + 1536 + 1024) * c.per_sm > sm_smem + 1024) continue;
+    per_sm = c.per_sm; a.nstage = c.nstage; a.s_bufs = c.s_bufs; a.kv_rows = c.kv_rows; a.tmem_cols = tc; stage = stg;
+    break;
   }
+  if (!per_sm) return pt::fail("pt_attention: Nk=%d does not fit in shared memory", Nk);
+  a.o_col = a.s_bufs * a.NKP;
+  if (make_map(&tk, k, (long long)B * Nk, (long long)heads * 64, k_stride, a.kv_rows)) return 1;
+  if (make_map(&tv, v, (long long)B * Nk, (long long)heads * 64, v_stride, a.kv_rows)) return 1;
   const size_t smem = 1024 + a.nstage * stage + ptile;
-  if (smem > sm_smem) return pt::fail("pt_attention: Nk=%d does not fit in shared memory", Nk);
   static size_t configured = 0;
   if (smem > configured) {
     PT_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -57,6 +57,82 @@ __global__ void pack_rows_kernel(PackArgs a) {
   }
 }
 
+// Same operation, one block per (sample, 32-channel slab) over the whole time axis: every channel row is read as one
+// contiguous run (T floats), the slab sits in shared memory, and the store side writes 64-byte channel runs per time
+// step (8 lanes x 4 bf16).  ~22 independent loads per thread keep enough bytes in flight to approach HBM speed.
+constexpr int kPackMaxT = 384;
+__global__ void __launch_bounds__(256) pack_rows_slab_kernel(PackArgs a) {
+  extern __shared__ float slab[];                      // [32][T + 1]
+  __shared__ float mask_s[kPackMaxT];
+  const int b = blockIdx.y, c0 = blockIdx.x * 32;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int ld = a.T + 1;
+  if (a.mode >= 1)
+    for (int t = tid; t < a.T; t += 256) mask_s[t] = a.mask[(size_t)b * a.T + t];
+  __syncthreads();
+  for (int i = w; i < 32; i += 8) {                    // warp w: channels c0 + w, c0 + w + 8, ...
+    const int c = c0 + i;
+    if (c < a.C) {
+      const float* src = a.src + ((size_t)b * a.C + c) * a.T;
+      const float* prd = (a.mode == 2) ? a.pred + ((size_t)b * a.C + c) * a.Tpred : nullptr;
+      // all of this lane's loads of the row are issued before the first use (kPackMaxT / 32 = 12 per operand)
+      float v[kPackMaxT / 32], pv[kPackMaxT / 32];
+#pragma unroll
+      for (int k = 0; k < kPackMaxT / 32; ++k) {
+        const int t = lane + 32 * k;
+        v[k] = (t < a.T) ? __ldg(src + t) : 0.f;
+      }
+      if (a.mode == 2) {
+        if (a.Tpred == a.T) {
+#pragma unroll
+          for (int k = 0; k < kPackMaxT / 32; ++k) {
+            const int t = lane + 32 * k;
+            pv[k] = (t < a.T) ? __ldg(prd + t) : 0.f;
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < kPackMaxT / 32; ++k) {
+            const int t = lane + 32 * k;
+            pv[k] = (t < a.T) ? interp_linear(prd, t, a.Tpred, a.T) : 0.f;
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kPackMaxT / 32; ++k) {
+        const int t = lane + 32 * k;
+        if (t < a.T) {
+          float x = v[k];
+          if (a.mode >= 1) {
+            const float m = mask_s[t];
+            x *= m;
+            if (a.mode == 2) x += pv[k] * (1.f - m);
+          }
+          slab[i * ld + t] = x;
+        }
+      }
+    } else {
+      for (int t = lane; t < a.T; t += 32) slab[i * ld + t] = 0.f;
+    }
+  }
+  __syncthreads();
+  const int cg = (tid & 7) * 4;                        // 4 consecutive channels of the slab
+  for (int t = tid >> 3; t < a.T; t += 32) {
+    __nv_bfloat16* d = a.dst + ((size_t)b * a.Tp + a.H + t) * a.Cp + a.c_off + c0 + cg;
+    const float v0 = slab[(cg + 0) * ld + t], v1 = slab[(cg + 1) * ld + t];
+    const float v2 = slab[(cg + 2) * ld + t], v3 = slab[(cg + 3) * ld + t];
+    if (c0 + cg + 3 < a.C && ((reinterpret_cast<uintptr_t>(d) & 7) == 0)) {
+      uint2 pk;
+      pk.x = pt::pack_bf16x2(v0, v1); pk.y = pt::pack_bf16x2(v2, v3);
+      *reinterpret_cast<uint2*>(d) = pk;
+    } else {
+      if (c0 + cg + 0 < a.C) d[0] = __float2bfloat16_rn(v0);
+      if (c0 + cg + 1 < a.C) d[1] = __float2bfloat16_rn(v1);
+      if (c0 + cg + 2 < a.C) d[2] = __float2bfloat16_rn(v2);
+      if (c0 + cg + 3 < a.C) d[3] = __float2bfloat16_rn(v3);
+    }
+  }
+}
+
 // mask channels: mode 0 -> one channel = mask (predictornet.py:85 cat([motion, mask]));
 //                mode 1 -> two channels one_hot(mask.long(), 2) (RTransformer.py:218): ch0 = (mask==0), ch1 = (mask==1)
 __global__ void pack_mask_kernel(const float* __restrict__ mask, __nv_bfloat16* __restrict__ dst, int B, int T, int Tp,
@@ -90,6 +166,26 @@ __global__ void blend_kernel(const float* __restrict__ known, const float* __res
     float k = known[i] * m;
     if (mask_pow == 2) k *= m;
     out[i] = k + interp_linear(pred + bc * Tpred, t, Tpred, T) * (1.f - m);
+  }
+}
+
+// fast path: no resampling (Tpred == T), T a multiple of 4, 16-byte aligned rows: one float4 per thread, 32-bit indexing
+__global__ void blend_vec4_kernel(const float4* __restrict__ known, const float* __restrict__ mask,
+                                  const float4* __restrict__ pred, float4* __restrict__ out, unsigned n4, unsigned T4,
+                                  unsigned C, int mask_pow) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+    const unsigned bc = i / T4, t4 = i - bc * T4, b = bc / C;
+    const float4 m = __ldg(reinterpret_cast<const float4*>(mask) + (size_t)b * T4 + t4);
+    const float4 k = __ldg(known + i), p = __ldg(pred + i);
+    float4 o;
+    if (mask_pow == 2) {
+      o.x = k.x * m.x * m.x + p.x * (1.f - m.x); o.y = k.y * m.y * m.y + p.y * (1.f - m.y);
+      o.z = k.z * m.z * m.z + p.z * (1.f - m.z); o.w = k.w * m.w * m.w + p.w * (1.f - m.w);
+    } else {
+      o.x = k.x * m.x + p.x * (1.f - m.x); o.y = k.y * m.y + p.y * (1.f - m.y);
+      o.z = k.z * m.z + p.z * (1.f - m.z); o.w = k.w * m.w + p.w * (1.f - m.w);
+    }
+    out[i] = o;
   }
 }
 
@@ -295,8 +391,13 @@ extern "C" int pt_pack_rows(const float* src, const float* mask, const float* pr
   if (mode == 2 && (!pred || pred_T <= 0)) return pt::fail("pt_pack_rows: mode 2 needs pred");
   if (c_off + C > Cp || H + T > Tp) return pt::fail("pt_pack_rows: destination too small");
   PackArgs a{src, mask, pred, (__nv_bfloat16*)dst_bf16, B, C, T, Tp, H, Cp, c_off, mode, pred_T};
-  dim3 grid((T + 31) / 32, (C + 31) / 32, B), block(32, 8);
-  pack_rows_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(a);
+  if (T <= kPackMaxT && B <= 65535) {
+    const size_t smem = (size_t)32 * (T + 1) * sizeof(float);   // <= 48 KB
+    pack_rows_slab_kernel<<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
+  } else {
+    dim3 grid((T + 31) / 32, (C + 31) / 32, B), block(32, 8);
+    pack_rows_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(a);
+  }
   PT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -318,8 +419,17 @@ extern "C" int pt_interp_blend(const float* known, const float* mask, const floa
   if (n <= 0) return 0;
   if (!known || !mask || !pred || !out) return pt::fail("pt_interp_blend: null pointer");
   if (mask_pow != 1 && mask_pow != 2) return pt::fail("pt_interp_blend: mask_pow must be 1 or 2");
-  const int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
-  blend_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(known, mask, pred, out, B, C, T, pred_T, mask_pow);
+  const bool aligned = ((reinterpret_cast<uintptr_t>(known) | reinterpret_cast<uintptr_t>(mask) |
+                         reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  if (pred_T == T && T % 4 == 0 && aligned && n / 4 < (1LL << 31)) {
+    const unsigned n4 = (unsigned)(n / 4);
+    const unsigned blocks = (n4 + 255) / 256;          // one float4 per thread: no loop-carried latency
+    blend_vec4_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const float4*)known, mask, (const float4*)pred,
+                                                                 (float4*)out, n4, (unsigned)(T / 4), (unsigned)C, mask_pow);
+  } else {
+    const int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+    blend_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(known, mask, pred, out, B, C, T, pred_T, mask_pow);
+  }
   PT_CUDA(cudaGetLastError());
   return 0;
 }

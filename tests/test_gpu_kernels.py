@@ -192,6 +192,33 @@ def test_pack_and_blend_match_torch():
     assert (out - (src * mask * mask + interp * (1 - mask))).abs().max() < 1e-5
 
 
+@pytest.mark.parametrize("B,Cc,T", [(5, 376, 180), (2, 129, 64), (3, 40, 36)])
+def test_pack_and_blend_same_length_paths(B, Cc, T):
+    """The slab pack kernel (modes 0/1/2) and the float4 blend path (pred already at T frames) vs torch."""
+    from probtalk_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator(device="cuda").manual_seed(B * 1000 + Cc + T)
+    src = torch.randn(B, Cc, T, device="cuda", generator=g)
+    pred = torch.randn(B, Cc, T, device="cuda", generator=g)
+    mask = (torch.rand(B, 1, T, device="cuda", generator=g) < 0.4).float()
+    H, Cp, c_off = 2, ((Cc + 63) // 64) * 64 + 64, 8
+    Tp = T + 5
+    for mode, ref in ((0, src), (1, src * mask), (2, src * mask + pred * (1 - mask))):
+        dst = torch.zeros(B, Tp, Cp, device="cuda", dtype=torch.bfloat16)
+        _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, dst.data_ptr(), B, Cc, T, Tp, H, Cp,
+                                  c_off, mode, _st()))
+        got = dst[:, H:H + T, c_off:c_off + Cc].float().transpose(1, 2)
+        assert torch.equal(got, ref.bfloat16().float())
+        chk = dst.clone()
+        chk[:, H:H + T, c_off:c_off + Cc] = 0
+        assert float(chk.abs().max()) == 0                  # halo rows and padding channels untouched
+    for pw in (1, 2):
+        out = torch.zeros(B, Cc, T, device="cuda")
+        _lib.check(L.pt_interp_blend(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, out.data_ptr(), B, Cc, T, pw, _st()))
+        ref = src * mask ** pw + pred * (1 - mask)
+        assert (out - ref).abs().max() < 1e-6
+
+
 @pytest.mark.parametrize("M,K", [(1000, 512), (128, 2048), (90112 // 8, 512)])
 @pytest.mark.parametrize("mode", [1, 2])
 def test_gemm_rownorm_cluster_epilogue(M, K, mode):
