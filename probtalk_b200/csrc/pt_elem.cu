@@ -61,7 +61,8 @@ __global__ void pack_rows_kernel(PackArgs a) {
 // contiguous run (T floats), the slab sits in shared memory, and the store side writes 64-byte channel runs per time
 // step (8 lanes x 4 bf16).  ~22 independent loads per thread keep enough bytes in flight to approach HBM speed.
 constexpr int kPackMaxT = 384;
-__global__ void __launch_bounds__(256) pack_rows_slab_kernel(PackArgs a) {
+template <int kIters>                                  // time steps per lane: T <= 32 * kIters
+__global__ void __launch_bounds__(256, 5) pack_rows_slab_kernel(PackArgs a) {
   extern __shared__ float slab[];                      // [32][T + 1]
   __shared__ float mask_s[kPackMaxT];
   const int b = blockIdx.y, c0 = blockIdx.x * 32;
@@ -75,30 +76,30 @@ __global__ void __launch_bounds__(256) pack_rows_slab_kernel(PackArgs a) {
     if (c < a.C) {
       const float* src = a.src + ((size_t)b * a.C + c) * a.T;
       const float* prd = (a.mode == 2) ? a.pred + ((size_t)b * a.C + c) * a.Tpred : nullptr;
-      // all of this lane's loads of the row are issued before the first use (kPackMaxT / 32 = 12 per operand)
-      float v[kPackMaxT / 32], pv[kPackMaxT / 32];
+      // all of this lane's loads of the row are issued before the first use
+      float v[kIters], pv[kIters];
 #pragma unroll
-      for (int k = 0; k < kPackMaxT / 32; ++k) {
+      for (int k = 0; k < kIters; ++k) {
         const int t = lane + 32 * k;
         v[k] = (t < a.T) ? __ldg(src + t) : 0.f;
       }
       if (a.mode == 2) {
         if (a.Tpred == a.T) {
 #pragma unroll
-          for (int k = 0; k < kPackMaxT / 32; ++k) {
+          for (int k = 0; k < kIters; ++k) {
             const int t = lane + 32 * k;
             pv[k] = (t < a.T) ? __ldg(prd + t) : 0.f;
           }
         } else {
 #pragma unroll
-          for (int k = 0; k < kPackMaxT / 32; ++k) {
+          for (int k = 0; k < kIters; ++k) {
             const int t = lane + 32 * k;
             pv[k] = (t < a.T) ? interp_linear(prd, t, a.Tpred, a.T) : 0.f;
           }
         }
       }
 #pragma unroll
-      for (int k = 0; k < kPackMaxT / 32; ++k) {
+      for (int k = 0; k < kIters; ++k) {
         const int t = lane + 32 * k;
         if (t < a.T) {
           float x = v[k];
@@ -166,6 +167,40 @@ __global__ void blend_kernel(const float* __restrict__ known, const float* __res
     float k = known[i] * m;
     if (mask_pow == 2) k *= m;
     out[i] = k + interp_linear(pred + bc * Tpred, t, Tpred, T) * (1.f - m);
+  }
+}
+
+// resampling path (pred has Tpred != T frames): one warp per (sample, channel) row, lanes stride the time axis, so the
+// row bases cost one division per warp and the two interpolation taps of neighbouring lanes share cache lines
+__global__ void __launch_bounds__(256) blend_rows_kernel(const float* __restrict__ known, const float* __restrict__ mask,
+                                                         const float* __restrict__ pred, float* __restrict__ out,
+                                                         unsigned rows, unsigned C, int T, int Tpred, int mask_pow) {
+  const unsigned row = blockIdx.x * 8u + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const unsigned b = row / C;
+  const float* k = known + (size_t)row * T;
+  const float* m = mask + (size_t)b * T;
+  const float* p = pred + (size_t)row * Tpred;
+  float* o = out + (size_t)row * T;
+  for (int t0 = 0; t0 < T; t0 += 128) {
+    float kv[4], mv[4], pv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = t0 + lane + 32 * j;
+      kv[j] = (t < T) ? __ldg(k + t) : 0.f;
+      mv[j] = (t < T) ? __ldg(m + t) : 0.f;
+      pv[j] = (t < T) ? interp_linear(p, t, Tpred, T) : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = t0 + lane + 32 * j;
+      if (t < T) {
+        float x = kv[j] * mv[j];
+        if (mask_pow == 2) x *= mv[j];
+        o[t] = x + pv[j] * (1.f - mv[j]);
+      }
+    }
   }
 }
 
@@ -393,7 +428,8 @@ extern "C" int pt_pack_rows(const float* src, const float* mask, const float* pr
   PackArgs a{src, mask, pred, (__nv_bfloat16*)dst_bf16, B, C, T, Tp, H, Cp, c_off, mode, pred_T};
   if (T <= kPackMaxT && B <= 65535) {
     const size_t smem = (size_t)32 * (T + 1) * sizeof(float);   // <= 48 KB
-    pack_rows_slab_kernel<<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
+    if (T <= 192) pack_rows_slab_kernel<6><<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
+    else pack_rows_slab_kernel<12><<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
   } else {
     dim3 grid((T + 31) / 32, (C + 31) / 32, B), block(32, 8);
     pack_rows_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(a);
@@ -426,6 +462,9 @@ extern "C" int pt_interp_blend(const float* known, const float* mask, const floa
     const unsigned blocks = (n4 + 255) / 256;          // one float4 per thread: no loop-carried latency
     blend_vec4_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const float4*)known, mask, (const float4*)pred,
                                                                  (float4*)out, n4, (unsigned)(T / 4), (unsigned)C, mask_pow);
+  } else if ((long long)B * C < (1LL << 31)) {
+    const unsigned rows = (unsigned)B * (unsigned)C;
+    blend_rows_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(known, mask, pred, out, rows, (unsigned)C, T, pred_T, mask_pow);
   } else {
     const int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
     blend_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(known, mask, pred, out, B, C, T, pred_T, mask_pow);
