@@ -172,6 +172,10 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if "PT_BENCH_NCCL_DEBUG" not in os.environ:
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+        else:
+            os.environ["NCCL_DEBUG"] = os.environ["PT_BENCH_NCCL_DEBUG"]
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
     B = args.batch
@@ -225,7 +229,10 @@ def run_ours(args):
 
     cpu = None
     if rank == 0 and not args.no_cpu:
-        cpu = cpu_baseline(args, (vq, pst, rst))
+        if world == 1:
+            cpu = cpu_baseline(args, (vq, pst, rst))
+        else:   # the CPU baseline is a rank-0, N = 1 measurement (torchrun also pins OMP to one thread per rank)
+            cpu = {"value": None, "unit": "clips/s", "cores": 0, "kind": "port", "sample": "measured at --gpus 1 only"}
     if rank == 0:
         pk = _peaks()
         ach = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
