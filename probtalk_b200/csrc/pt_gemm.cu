@@ -70,6 +70,7 @@ struct GemmKernelArgs {
   const int* labels;              // class per sample (row / label_rows) or null (class 0)
   int label_rows;
   int norm_classes;
+  int tma_store;                  // tmap_o describes the output as a dense bf16 [M, n_valid] matrix: 32 x 32 boxes are stored by TMA
 };
 
 __device__ __forceinline__ float apply_act(float v, int act, float slope) {
@@ -142,7 +143,7 @@ __device__ __forceinline__ void welford_merge(float& n, float& mean, float& m2, 
 template <int BN, bool kRowNorm, int kCL, bool k2 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-            const GemmKernelArgs p) {
+            const __grid_constant__ CUtensorMap tmap_o, const GemmKernelArgs p) {
   using C = Cfg<BN, k2>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -154,7 +155,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   // epilogue staging lives in STATIC shared memory so the compiler emits LDS/STS (pointers carved from the
   // dynamic buffer lose their address space and become slow generic loads)
-  __shared__ __align__(16) uint8_t tile_s[kEpiWarps][32 * 64];
+  __shared__ __align__(1024) uint8_t tile_s[kEpiWarps][32 * 64];   // PT_TILE_OFF == TMA SWIZZLE_64B, so a tile can be stored by TMA
   __shared__ __align__(16) float bias_s[kRowNorm ? 1 : kEpiWarps][BN / 2];   // this warp's 128 (or 64) bias columns of the current tile
   __shared__ long long rowoff_s[kRowNorm ? 1 : kEpiWarps][64];
   __shared__ __align__(16) float rn_bias_s[kRowNorm ? BN : 4];               // row-norm: the CTA's 256 bias columns
@@ -181,6 +182,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     pt::tma_prefetch_desc(&tmap_a);
     pt::tma_prefetch_desc(&tmap_b);
+    if (p.tma_store) pt::tma_prefetch_desc(&tmap_o);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], kCL); }
@@ -467,6 +469,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             pk[2 * i] = cvt_bf16x2(y0, y1, false);
             pk[2 * i + 1] = cvt_bf16x2(y2, y3, false);
           }
+          if (p.tma_store) {
+            if (lane == 0) pt::bulk_wait_read_all();     // the previous box has been read out of the tile
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(tile_row[i]) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            pt::fence_async_smem();
+            __syncwarp();
+            if (lane == 0) { pt::tma_store_2d(&tmap_o, tile, n0 + cb + 32 * c, m0 + q * 32); pt::bulk_commit(); }
+            continue;
+          }
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < 4; ++i)
@@ -477,6 +490,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             if (ro4[j] >= 0)
               *(reinterpret_cast<uint4*>(outp + ro4[j] + 32 * c) + pc) = *reinterpret_cast<const uint4*>(tile_in[j]);
           }
+        }
+        if (resp && p.tma_store) {                       // the next tile's residual transposition reuses the tile
+          if (lane == 0) pt::bulk_wait_read_all();
+          __syncwarp();
         }
         continue;
       }
@@ -545,17 +562,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             pk[2 * i] = cvt_bf16x2(a0, a1, lean_relu);
             pk[2 * i + 1] = cvt_bf16x2(a2, a3, lean_relu);
           }
+          if (p.tma_store) {
+            // the tile leaves through the TMA: no LDS / STG, no per-row predicates (the tensor map clips at M)
+            if (lane == 0) pt::bulk_wait_read_all();     // the previous box has been read out of the tile
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(tile_row[i]) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            pt::fence_async_smem();
+            __syncwarp();
+            if (lane == 0) { pt::tma_store_2d(&tmap_o, tile, n, m0 + q * 32); pt::bulk_commit(); }
+            continue;
+          }
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, i)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            *reinterpret_cast<uint4*>(tile_row[i]) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const int rr = pr + 8 * j;
             if (ro4[j] >= 0)
               *(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro4[j] + n) + pc) =
-                  *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pc));
+                  *reinterpret_cast<const uint4*>(tile_in[j]);
           }
           continue;
         }
@@ -695,6 +723,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       if (lane == 0) release_acc(acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (p.tma_store && lane == 0) pt::bulk_wait_all();   // this warp's TMA stores are complete before the CTA may exit
   }
   pt::tc_fence_before();
   __syncthreads();
@@ -739,8 +768,25 @@ int make_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols,
   return 0;
 }
 
+// output map for the epilogue's TMA stores: bf16 [rows, cols] with `pitch` elements per row, 32 x 32 boxes in the
+// SWIZZLE_64B layout that PT_TILE_OFF produces
+int make_tmap_out(CUtensorMap* tm, void* base, long long rows, long long cols, long long pitch) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return pt::fail("cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  cuuint32_t box[2] = {32u, 32u};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return pt::fail("cuTensorMapEncodeTiled failed (%d) for the output map rows=%lld cols=%lld pitch=%lld", (int)r, rows,
+                    cols, pitch);
+  return 0;
+}
+
 template <int BN, int CL>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, false, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
@@ -751,7 +797,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& k
   int clusters = sms / CL;
   if (tiles < clusters) clusters = tiles;
   if constexpr (CL == 1) {
-    gemm_kernel<BN, false, 1><<<clusters, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, ka);
+    gemm_kernel<BN, false, 1><<<clusters, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, to, ka);
     PT_CUDA(cudaGetLastError());
   } else {
     cudaLaunchConfig_t cfg = {};
@@ -763,13 +809,13 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& k
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, ka));
+    PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, to, ka));
   }
   return 0;
 }
 
 // cta_group::2 variant: pairs of CTAs, one 256-row x 256-column tile per pair step
-int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   using Cf = Cfg<256, true>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -788,12 +834,12 @@ int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelAr
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, false, 1, true>, ta, tb, ka));
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, false, 1, true>, ta, tb, to, ka));
   return 0;
 }
 
 // row-norm variant: clusters of two CTAs, one 128-row tile per cluster step
-int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmem));
@@ -810,7 +856,7 @@ int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKerne
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true, 1>, ta, tb, ka));
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true, 1>, ta, tb, to, ka));
   return 0;
 }
 
@@ -901,10 +947,25 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   ka.act = d->act; ka.slope = d->slope; ka.m_tiles = (d->M + BM - 1) / BM;
   ka.row_norm = d->row_norm; ka.norm_a = d->norm_a; ka.norm_b = d->norm_b; ka.labels = d->labels; ka.label_rows = d->label_rows; ka.norm_classes = d->norm_classes;
   cudaStream_t st = (cudaStream_t)stream;
-  if (d->row_norm) return launch_rownorm(ta, tb, ka, sms, st);
-  if (two_cta) return launch_2cta(ta, tb, ka, sms, st);
-  if (BN == 128) return launch<128, 1>(ta, tb, ka, sms, st);
-  if (CL == 4) return launch<256, 4>(ta, tb, ka, sms, st);
-  if (CL == 2) return launch<256, 2>(ta, tb, ka, sms, st);
-  return launch<256, 1>(ta, tb, ka, sms, st);
+  // Dense bf16 row-major outputs (every row of every sample valid, one pitch) are stored by TMA from the epilogue's
+  // swizzled staging tiles; anything else (ragged rows, fp32, channel-major) keeps the LDS/STG path.
+  CUtensorMap to = ta;
+  ka.tma_store = 0;
+  {
+    static const bool off = getenv("PT_GEMM_TMA_STORE") && atoi(getenv("PT_GEMM_TMA_STORE")) == 0;
+    const bool dense = !d->out_f32 && d->ocs == 1 && d->t_valid == d->rows_per_sample &&
+                       (d->M <= d->rows_per_sample || d->oss == (long long)d->rows_per_sample * d->ors) &&
+                       d->ors >= d->n_valid && (d->ors % 8) == 0 &&
+                       (d->n_valid % 8) == 0 && (reinterpret_cast<uintptr_t>(d->out) & 15) == 0;
+    if (!off && dense) {
+      if (make_tmap_out(&to, d->out, d->M, d->n_valid, d->ors)) return 1;
+      ka.tma_store = 1;
+    }
+  }
+  if (d->row_norm) return launch_rownorm(ta, tb, to, ka, sms, st);
+  if (two_cta) return launch_2cta(ta, tb, to, ka, sms, st);
+  if (BN == 128) return launch<128, 1>(ta, tb, to, ka, sms, st);
+  if (CL == 4) return launch<256, 4>(ta, tb, to, ka, sms, st);
+  if (CL == 2) return launch<256, 2>(ta, tb, to, ka, sms, st);
+  return launch<256, 1>(ta, tb, to, ka, sms, st);
 }
