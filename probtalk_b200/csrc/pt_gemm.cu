@@ -402,10 +402,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
               const uint4 x = *reinterpret_cast<const uint4*>(tile_row[i]);
               const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {          // bf16 -> fp32 is a 16-bit shift: low half << 16, high half masked
-                f[c][8 * i + 2 * j] += __uint_as_float(w4[j] << 16);
-                f[c][8 * i + 2 * j + 1] += __uint_as_float(w4[j] & 0xffff0000u);
-              }
+              for (int j = 0; j < 4; ++j)            // bf16 -> fp32 is a 16-bit shift: low half << 16, high half masked
+                add2(f[c][8 * i + 2 * j], f[c][8 * i + 2 * j + 1], __uint_as_float(w4[j] << 16),
+                     __uint_as_float(w4[j] & 0xffff0000u));
             }
           }
 #pragma unroll
