@@ -65,18 +65,6 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
   return d;
 }
 
-// smem matrix descriptor, MN-major operand, SWIZZLE_128B: 64 MN-elements (128 B) per row, rows = K index;
-// SBO = stride between groups of 8 K-rows (1024 B); LBO = stride between 64-element MN atoms (single atom here)
-__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
-  d |= static_cast<uint64_t>(1024 >> 4) << 16;
-  d |= static_cast<uint64_t>(1024 >> 4) << 32;
-  d |= static_cast<uint64_t>(1) << 46;
-  d |= static_cast<uint64_t>(2) << 61;
-  return d;
-}
-
 __global__ void __launch_bounds__(kThreadsTc, 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const AttnTcArgs a) {
@@ -173,7 +161,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             pt::tc_fence_after();
             for (int j = 0; j < ksteps; ++j)
               pt::umma_bf16(tmem_o, pt::umma_desc_sw128(sp + (j >> 2) * kAtomBytes + (j & 3) * 32),
-                            umma_desc_sw128_mn(sv + j * 2048), idesc_o, j ? 1u : 0u);
+                            pt::umma_desc_sw128_mn(sv + j * 2048), idesc_o, j ? 1u : 0u);
             pt::umma_commit(o_full);
             pt::umma_commit(&v_empty[st]);
             ++ip; progressed = true;

@@ -70,6 +70,7 @@ struct GemmKernelArgs {
   const int* labels;              // class per sample (row / label_rows) or null (class 0)
   int label_rows;
   int norm_classes;
+  int res_mma;                    // row-norm: the bf16 residual tile is added by the tensor core (identity x residual), tmap_r
   int tma_store;                  // tmap_o describes the output as a dense bf16 [M, n_valid] matrix: 32 x 32 boxes are stored by TMA
 };
 
@@ -143,7 +144,8 @@ __device__ __forceinline__ void welford_merge(float& n, float& mean, float& m2, 
 template <int BN, bool kRowNorm, int kCL, bool k2 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-            const __grid_constant__ CUtensorMap tmap_o, const GemmKernelArgs p) {
+            const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_r,
+            const GemmKernelArgs p) {
   using C = Cfg<BN, k2>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -183,9 +185,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     pt::tma_prefetch_desc(&tmap_a);
     pt::tma_prefetch_desc(&tmap_b);
     if (p.tma_store) pt::tma_prefetch_desc(&tmap_o);
+    if (p.res_mma) pt::tma_prefetch_desc(&tmap_r);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], 1); pt::mbar_init(&empty[i], kCL); }
+    const uint32_t full_count = (kRowNorm && p.res_mma) ? 2u : 1u;
+    for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], full_count); pt::mbar_init(&empty[i], kCL); }
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], (k2 ? 2 : 1) * kEpiWarps); }
     if constexpr (kRowNorm) { pt::mbar_init(&stats_bar[0], kEpiWarps); pt::mbar_init(&stats_bar[1], kEpiWarps); }
     pt::fence_mbar_init();
@@ -204,7 +208,63 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   // accumulators across the LayerNorm.  128 * 40 + 256 * 232 = 64512 = 384 * 168, what the kernel is launched with.
   if (warp < kEpiWarp0) {
    if constexpr (kRowNorm) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-   if (warp == 0) {
+   if (warp == 0 && kRowNorm && p.res_mma) {
+    // ------------------------------------------------------------ TMA producer, residual-through-MMA flavour
+    // After the K blocks of a tile come two more pipeline slots that make the tensor core add the bf16 residual:
+    //   acc[m, n] += sum_k I[m, k] * R[k, n],  k = row of the 128-row tile (two blocks of 64).
+    // The B slot gets the residual rows as four [64 rows x 64 columns] boxes, which is exactly the MN-major operand
+    // layout (rows = K); the A slot gets the matching 128 x 64 block of the identity, written by warp 3 (below).
+    // 1.0 * bf16 accumulates exactly in fp32, and the epilogue no longer touches the residual at all.
+    // full[] barriers take two arrivals in this flavour: the producer's (with the TMA byte count) and the filler's.
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
+        const int m0 = tile_m0(tile), n0 = tile_n0(tile);
+        for (int kk = 0; kk < p.K_iters + 2; ++kk) {
+          pt::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+          if (kk < p.K_iters) {
+            const int tap = kk / p.c_iters, cc = kk - tap * p.c_iters;
+            pt::mbar_expect_tx(&full[stage], C::kStageBytes);
+            pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
+            pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
+            pt::mbar_arrive(&full[stage]);                 // stands in for the filler's arrival
+          } else {
+            const int kb = kk - p.K_iters;
+            pt::mbar_expect_tx(&full[stage], C::kBBytes);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              pt::tma_load_2d(sa + C::kABytes + j * 8192, &tmap_r, &full[stage], n0 + 64 * j, m0 + 64 * kb);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+   } else if (warp == 3 && kRowNorm && p.res_mma) {
+    // ------------------------------------------------------------ identity filler (see above)
+    int stage = 0; uint32_t phase = 0;
+    for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
+      // walk the K-block slots in step with the producer (parity waits are only valid one phase ahead)
+      for (int kk = 0; kk < p.K_iters; ++kk) {
+        pt::mbar_wait(&empty[stage], phase ^ 1);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      for (int kb = 0; kb < 2; ++kb) {
+        pt::mbar_wait(&empty[stage], phase ^ 1);
+        uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+        for (int i = lane; i < (int)(C::kABytes / 16); i += 32) reinterpret_cast<uint4*>(sa)[i] = make_uint4(0, 0, 0, 0);
+        __syncwarp();
+        for (int r = lane; r < 64; r += 32) {              // row m = 64 kb + r holds its 1.0 at column r of this block
+          const int m = 64 * kb + r;
+          *reinterpret_cast<uint16_t*>(sa + m * 128 + ((((r >> 3) ^ (m & 7)) & 7) << 4) + (r & 7) * 2) = 0x3F80;
+        }
+        pt::fence_async_smem();
+        __syncwarp();
+        if (lane == 0) pt::mbar_arrive(&full[stage]);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+   } else if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
@@ -266,9 +326,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           } else {
             if constexpr (kCL == 1) pt::umma_commit(&empty[stage]);   // slot reusable once these MMAs have read it
             else pt::umma_commit_mc(&empty[stage], kMcMask);          // ... in every CTA that multicasts into it
-            if (kk == p.K_iters - 1) pt::umma_commit(&tmem_full[acc]);
+            if (kk == p.K_iters - 1 && !(kRowNorm && p.res_mma)) pt::umma_commit(&tmem_full[acc]);
           }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        if constexpr (kRowNorm) {
+          if (p.res_mma) {
+            // acc += I * R: A = identity block (K-major), B = residual rows (MN-major, one 64-column atom per MMA)
+            constexpr uint32_t idesc_r = pt::umma_idesc_bf16(BM, BN) | (1u << 16);
+            for (int kb = 0; kb < 2; ++kb) {
+              pt::mbar_wait(&full[stage], phase);
+              pt::tc_fence_after();
+              const uint32_t sa = pt::smem_u32(smem + (size_t)stage * C::kStageBytes);
+              const uint32_t sb = sa + C::kABytes;
+              // one N = 256 instruction per K step: the four 64-column atoms of B are 8 KB apart (LBO)
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128_mn(sb + k * 2048, 8192), idesc_r, 1u);
+              pt::umma_commit(&empty[stage]);
+              if (kb == 1) pt::umma_commit(&tmem_full[acc]);
+              if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+            }
+          }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
@@ -341,7 +420,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         constexpr unsigned kFull = 0xffffffffu;
         const int cb = half * (BN / 2);
         const int obase_m = row_ok ? (int)obase + n0 + cb : -1;
-        const __nv_bfloat16* resp = static_cast<const __nv_bfloat16*>(p.residual);
+        const __nv_bfloat16* resp = p.res_mma ? nullptr : static_cast<const __nv_bfloat16*>(p.residual);
         // residual: all 16 loads of this lane (4 chunks x 4 row segments of 64 bytes) leave before the accumulator wait
         uint4 xr[kChunks][4];
         if (resp) {
@@ -767,25 +846,30 @@ int make_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols,
   return 0;
 }
 
-// output map for the epilogue's TMA stores: bf16 [rows, cols] with `pitch` elements per row, 32 x 32 boxes in the
-// SWIZZLE_64B layout that PT_TILE_OFF produces
-int make_tmap_out(CUtensorMap* tm, void* base, long long rows, long long cols, long long pitch) {
+// bf16 [rows, cols] matrix with `pitch` elements per row, boxes of box_cols x box_rows:
+//   * output map for the epilogue's TMA stores: 32 x 32 boxes in the SWIZZLE_64B layout that PT_TILE_OFF produces
+//   * residual map for the residual-through-MMA path: 64 x 64 boxes, SWIZZLE_128B
+int make_tmap_box(CUtensorMap* tm, const void* base, long long rows, long long cols, long long pitch, int box_cols,
+                  int box_rows, CUtensorMapSwizzle swz) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return pt::fail("cuTensorMapEncodeTiled entry point not found");
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
-  cuuint32_t box[2] = {32u, 32u};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
-    return pt::fail("cuTensorMapEncodeTiled failed (%d) for the output map rows=%lld cols=%lld pitch=%lld", (int)r, rows,
-                    cols, pitch);
+    return pt::fail("cuTensorMapEncodeTiled failed (%d) for a %dx%d-box map rows=%lld cols=%lld pitch=%lld", (int)r,
+                    box_cols, box_rows, rows, cols, pitch);
   return 0;
+}
+int make_tmap_out(CUtensorMap* tm, void* base, long long rows, long long cols, long long pitch) {
+  return make_tmap_box(tm, base, rows, cols, pitch, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
 template <int BN, int CL>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, false, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
@@ -796,7 +880,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, 
   int clusters = sms / CL;
   if (tiles < clusters) clusters = tiles;
   if constexpr (CL == 1) {
-    gemm_kernel<BN, false, 1><<<clusters, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, to, ka);
+    gemm_kernel<BN, false, 1><<<clusters, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, to, tr, ka);
     PT_CUDA(cudaGetLastError());
   } else {
     cudaLaunchConfig_t cfg = {};
@@ -808,13 +892,13 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, 
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, to, ka));
+    PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, to, tr, ka));
   }
   return 0;
 }
 
 // cta_group::2 variant: pairs of CTAs, one 256-row x 256-column tile per pair step
-int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   using Cf = Cfg<256, true>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -833,12 +917,12 @@ int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap&
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, false, 1, true>, ta, tb, to, ka));
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, false, 1, true>, ta, tb, to, tr, ka));
   return 0;
 }
 
 // row-norm variant: clusters of two CTAs, one 128-row tile per cluster step
-int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
+int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmem));
@@ -855,7 +939,7 @@ int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorM
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true, 1>, ta, tb, to, ka));
+  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true, 1>, ta, tb, to, tr, ka));
   return 0;
 }
 
@@ -961,10 +1045,23 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
       ka.tma_store = 1;
     }
   }
-  if (d->row_norm) return launch_rownorm(ta, tb, to, ka, sms, st);
-  if (two_cta) return launch_2cta(ta, tb, to, ka, sms, st);
-  if (BN == 128) return launch<128, 1>(ta, tb, to, ka, sms, st);
-  if (CL == 4) return launch<256, 4>(ta, tb, to, ka, sms, st);
-  if (CL == 2) return launch<256, 2>(ta, tb, to, ka, sms, st);
-  return launch<256, 1>(ta, tb, to, ka, sms, st);
+  // Row-norm with a dense bf16 residual: the residual tile rides through the pipeline and is added by the tensor core
+  CUtensorMap tr = ta;
+  ka.res_mma = 0;
+  if (d->row_norm && d->residual && !d->res_f32) {
+    static const bool off = getenv("PT_GEMM_RES_MMA") && atoi(getenv("PT_GEMM_RES_MMA")) == 0;
+    const bool dense = d->t_valid == d->rows_per_sample &&
+                       (d->M <= d->rows_per_sample || d->rss == (long long)d->rows_per_sample * d->rrs) &&
+                       d->rrs >= 512 && (d->rrs % 8) == 0 && (reinterpret_cast<uintptr_t>(d->residual) & 15) == 0;
+    if (!off && dense) {
+      if (make_tmap_box(&tr, d->residual, d->M, 512, d->rrs, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return 1;
+      ka.res_mma = 1;
+    }
+  }
+  if (d->row_norm) return launch_rownorm(ta, tb, to, tr, ka, sms, st);
+  if (two_cta) return launch_2cta(ta, tb, to, tr, ka, sms, st);
+  if (BN == 128) return launch<128, 1>(ta, tb, to, tr, ka, sms, st);
+  if (CL == 4) return launch<256, 4>(ta, tb, to, tr, ka, sms, st);
+  if (CL == 2) return launch<256, 2>(ta, tb, to, tr, ka, sms, st);
+  return launch<256, 1>(ta, tb, to, tr, ka, sms, st);
 }
