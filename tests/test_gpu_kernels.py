@@ -126,6 +126,35 @@ def test_attention(Nq, Nk):
     assert (out.float() - ref).abs().max() < 0.03
 
 
+@pytest.mark.parametrize("Nq,Nk", [(88, 88), (88, 22), (180, 180)])
+def test_attention_many_units_repeated(Nq, Nk):
+    """Bench-sized launches (every persistent CTA walks ~28 units, all buffer rings wrap many times), repeated: guards
+    the mbarrier protocol of the pipelined kernel (a parity-aliasing bug only showed at this size) and run-to-run
+    determinism."""
+    from probtalk_b200 import _lib
+    B, Hh, D = 512, 8, 64
+    g = torch.Generator(device="cuda").manual_seed(Nq + Nk)
+    q = torch.randn(B * Nq, Hh * D, device="cuda", generator=g).bfloat16()
+    kv = torch.randn(B * Nk, 2 * Hh * D, device="cuda", generator=g).bfloat16()
+    outs = []
+    for _ in range(6):
+        out = torch.zeros(B * Nq, Hh * D, device="cuda", dtype=torch.bfloat16)
+        _lib.check(_lib.lib().pt_attention(q.data_ptr(), Hh * D, kv.data_ptr(), 2 * Hh * D, kv.data_ptr() + 2 * Hh * D,
+                                           2 * Hh * D, out.data_ptr(), Hh * D, B, Hh, D, Nq, Nk, 1.0 / math.sqrt(D), _st()))
+        outs.append(out)
+    torch.cuda.synchronize()
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])
+    sl = slice(0, 16 * Nq)                                  # reference on the first 16 samples and the last one
+    for lo, hi, blo, bhi in ((0, 16 * Nq, 0, 16), ((B - 1) * Nq, B * Nq, B - 1, B)):
+        nb = bhi - blo
+        qf = q[lo:hi].float().view(nb, Nq, Hh, D).transpose(1, 2)
+        kf = kv[blo * Nk:bhi * Nk, :Hh * D].float().view(nb, Nk, Hh, D).transpose(1, 2)
+        vf = kv[blo * Nk:bhi * Nk, Hh * D:].float().view(nb, Nk, Hh, D).transpose(1, 2)
+        ref = (torch.softmax(qf @ kf.transpose(-1, -2) / math.sqrt(D), -1) @ vf).transpose(1, 2).reshape(nb * Nq, Hh * D)
+        assert (outs[0][lo:hi].float() - ref).abs().max() < 0.03
+
+
 def test_layernorm_kernels_and_embed():
     from probtalk_b200 import _lib
     L = _lib.lib()
