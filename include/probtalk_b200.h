@@ -126,6 +126,15 @@ int pt_pack_rows(const float* src, const float* mask, const float* pred, int pre
 int pt_pack_mask(const float* mask, void* dst_bf16, int B, int T, int Tp, int H, int Cp, int c_off, int onehot,
                  void* stream);
 
+/* Pose post-processing: normalised network output -> SMPL-X axis-angle parameters in one pass.
+ * Replaces the sequence of scripts/demo.py:183-205:
+ *   denormalize (nets/utils.py:27-43; mean / std already reordered to the 'fbhe' channel order, NULL = skip)
+ *   -> per joint rotation_6d_to_matrix -> matrix_to_axis_angle (data_utils/rotation_conversion.py:512-534, 433-447,
+ *      97-119, 481-509) -> cat(expression) -> part2full (data_utils/lower_body.py:66-83, lower27 = its `lp` row).
+ *   poses [B, 6*n_joints + n_expr, T] fp32 channel-first  ->  out [B, T, 3*n_joints + n_expr + 27] fp32. */
+int pt_pose_postprocess(const float* poses, const float* mean, const float* stdv, const float* lower27, float* out, int B,
+                        int T, int n_joints, int n_expr, void* stream);
+
 /* out = known * mask^mask_pow + interp(pred, T) * (1 - mask), all fp32 channel-first [B, C, T] (pred [B, C, pred_T]).
  * mask_pow = 2: predictor.py:445-446 ((gt*mask)*mask + ...);  mask_pow = 1: refiner.py:553. */
 int pt_interp_blend(const float* known, const float* mask, const float* pred, int pred_T, float* out, int B, int C,
