@@ -248,7 +248,7 @@ def test_pack_and_blend_same_length_paths(B, Cc, T):
         assert (out - ref).abs().max() < 1e-6
 
 
-@pytest.mark.parametrize("M,K", [(1000, 512), (128, 2048), (90112 // 8, 512)])
+@pytest.mark.parametrize("M,K", [(1000, 512), (128, 2048), (90112 // 8, 512), (90112 // 8 + 77, 2048), (22000, 1024)])
 @pytest.mark.parametrize("mode", [1, 2])
 def test_gemm_rownorm_cluster_epilogue(M, K, mode):
     """Fused LayerNorm epilogue (2-CTA cluster exchanging row statistics through DSMEM) vs torch."""
