@@ -126,6 +126,17 @@ int pt_pack_rows(const float* src, const float* mask, const float* pred, int pre
 int pt_pack_mask(const float* mask, void* dst_bf16, int B, int T, int Tp, int H, int Cp, int c_off, int onehot,
                  void* stream);
 
+/* Feature statistics for the Frechet gesture distance: mean (np.mean(axis=0)) and unbiased covariance
+ * (np.cov(rowvar=False)) of N feature vectors, fp64, deterministic (fixed reduction order, no atomics).
+ * Replaces the statistics half of EmbeddingSpaceEvaluator.get_scores / frechet_distance (evaluation/FGD.py:172-176);
+ * the 128 x 128 matrix square root of calculate_frechet_distance (:190-257) stays on the host.
+ *   feats [N, D] fp32 row-major, 2 <= N, 1 <= D <= 128;  mean_out [D], cov_out [D, D] fp64 (device memory).
+ * The per-chunk partial sums need scratch memory: the caller provides `workspace` (device memory, 8-byte aligned,
+ * at least pt_feature_stats_workspace_bytes(D) bytes; contents need not be initialised and are clobbered). */
+long long pt_feature_stats_workspace_bytes(int D);
+int pt_feature_stats(const float* feats, int N, int D, double* mean_out, double* cov_out, void* workspace,
+                     long long workspace_bytes, void* stream);
+
 /* Pose post-processing: normalised network output -> SMPL-X axis-angle parameters in one pass.
  * Replaces the sequence of scripts/demo.py:183-205:
  *   denormalize (nets/utils.py:27-43; mean / std already reordered to the 'fbhe' channel order, NULL = skip)

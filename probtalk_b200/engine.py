@@ -809,3 +809,74 @@ class RefinerPlan:
                 self.graph = g
             self.graph.replay()
         return self.out
+
+
+# ----------------------------------------------------------------------------------------------
+# FGD feature extractor  (reference: EmbeddingNet.extract -> PoseEncoderConv.forward, nets/embedding_net.py:56-95,
+#                         147-150; ConvNormRelu :29-53)  -- SURVEY.md 8(f)3
+# ----------------------------------------------------------------------------------------------
+
+class EmbeddingWeights:
+    """Folded weights of PoseEncoderConv(length=90, dim): four VALID convolutions (k3, k3, k4 s2, k3; BatchNorm folded,
+    LeakyReLU 0.2) and the MLP 1280 -> 512 -> 256 -> 128 -> fc_mu 128.  `nn.LeakyReLU(True)` in the MLP is
+    negative_slope = 1.0, i.e. the identity (embedding_net.py:71-77), reproduced as such."""
+
+    def __init__(self, sd, device, prefix="pose_encoder."):
+        g = lambda k: sd[prefix + k]
+        self.dim = g("net.0.0.weight").shape[1]
+        self.c1 = prep_conv(g("net.0.0.weight"), g("net.0.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.0.1"))
+        self.c2 = prep_conv(g("net.1.0.weight"), g("net.1.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.1.1"), cin_pad=64)
+        self.c3 = prep_conv(g("net.2.0.weight"), g("net.2.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.2.1"))
+        self.c4 = prep_conv(g("net.3.weight"), g("net.3.bias"), device)
+        # flatten(1) of [B, 32, 40] is channel-major; our rows are [B, 40, 64]: W'[n, t*64 + c] = W[n, c*40 + t]
+        w = g("out_net.0.weight").float()                                   # [512, 1280]
+        s0, h0 = _bn_scale_shift(sd, prefix + "out_net.1")
+        wp = torch.zeros(512, 40, 64)
+        wp[:, :, :32] = w.view(512, 32, 40).permute(0, 2, 1)
+        self.l1 = prep_linear(wp.reshape(512, 2560) * s0[:, None], g("out_net.0.bias").float() * s0 + h0, device)
+        s1, h1 = _bn_scale_shift(sd, prefix + "out_net.4")
+        self.l2 = prep_linear(g("out_net.3.weight").float() * s1[:, None], g("out_net.3.bias").float() * s1 + h1, device)
+        self.l3 = prep_linear(g("out_net.6.weight"), g("out_net.6.bias"), device)
+        self.mu = prep_linear(g("fc_mu.weight"), g("fc_mu.bias"), device)
+
+
+class EmbeddingPlan:
+    """poses [B, dim, 90] fp32 (channel-first, as pushed by test_holisticbody.py:279) -> features [B, 128] fp32."""
+
+    def __init__(self, W: EmbeddingWeights, B, dev="cuda"):
+        self.W, self.B = W, B
+        p = self.plan = Plan(dev)
+        L = _lib.lib()
+        T = 90
+        self.poses = torch.zeros(B, W.dim, T, dtype=F32, device=dev)
+        x0 = RowBuf(B, T, _ceil(W.dim, 64), 0, device=dev)
+        p.call(L.pt_pack_rows, self.poses.data_ptr(), None, None, 0, x0.t.data_ptr(), B, W.dim, T, x0.Tp, 0, x0.C, 0, 0)
+        h1, h2 = RowBuf(B, 88, 64, 0, device=dev), RowBuf(B, 86, 64, 0, device=dev)
+        h3, h4 = RowBuf(B, 42, 64, 0, device=dev), RowBuf(B, 40, 64, 0, device=dev)
+
+        def valid_conv(x, w, out, act):                  # k3, stride 1, no padding: out[t] = sum_j x[t + j]
+            p.gemm(x.t, x.B * x.Tp, x.C, w, out.t, M=x.B * x.Tp, C_=x.C, s=1, base_row=0, rows_per_sample=x.Tp,
+                   t_valid=out.T, oss=out.Tp * out.C, ors=out.C, act=act, slope=0.2)
+
+        valid_conv(x0, W.c1, h1, ACT_LEAKY)
+        valid_conv(h1, W.c2, h2, ACT_LEAKY)
+        # k4, stride 2, no padding: rows viewed as [Tp / 2, 2 C]; tap j = row t + j / 2, column half j % 2
+        p.gemm(h2.t, B * h2.Tp, h2.C, W.c3, h3.t, M=B * h2.Tp // 2, C_=h2.C, s=2, base_row=0, rows_per_sample=h2.Tp // 2,
+               t_valid=h3.T, oss=h3.Tp * h3.C, ors=h3.C, act=ACT_LEAKY, slope=0.2)
+        valid_conv(h3, W.c4, h4, ACT_NONE)
+        z = lambda n, dt=BF16: torch.zeros(B, n, dtype=dt, device=dev)
+        f1, f2, f3 = z(512), z(256), z(128)
+        self.out = z(128, F32)
+        p.linear(h4.t, B, W.l1, f1)                      # A = the [B, 40 * 64] view of the conv output
+        p.linear(f1, B, W.l2, f2)
+        p.linear(f2, B, W.l3, f3)
+        p.linear(f3, B, W.mu, self.out)
+        self.keep = [x0, h1, h2, h3, h4, f1, f2, f3]
+
+    def extract(self, poses):
+        """poses [n <= B, dim, 90] -> [n, 128] (a view of the plan's output buffer; clone to keep it)."""
+        n = poses.shape[0]
+        assert n <= self.B and tuple(poses.shape[1:]) == (self.W.dim, 90)
+        self.poses[:n].copy_(poses)
+        self.plan.run()
+        return self.out[:n]

@@ -1,0 +1,87 @@
+"""Frechet gesture distance evaluator, mirroring evaluation/FGD.py's EmbeddingSpaceEvaluator.
+
+* feature extraction: ``EmbeddingPlan`` (engine.py) runs PoseEncoderConv (nets/embedding_net.py:56-95) on the GEMM engine;
+* statistics: ``feature_stats`` -> ``pt_feature_stats`` (fp64 mean / covariance, deterministic);
+* distance: ``frechet_distance`` = calculate_frechet_distance (evaluation/FGD.py:190-257) on the host -- a 128 x 128
+  matrix square root, host logic like in the reference.
+CUDA tensors only; the library must be present (no CPU fallback).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def feature_stats(feats: torch.Tensor):
+    """feats [N, D] fp32 CUDA -> (mean [D], cov [D, D]) fp64 CUDA tensors; np.mean(axis=0) / np.cov(rowvar=False)."""
+    if not feats.is_cuda:
+        raise _lib.PtError("probtalk_b200.evaluation needs CUDA tensors (no CPU fallback)")
+    assert feats.dim() == 2 and feats.dtype == torch.float32
+    feats = feats.contiguous()
+    N, D = feats.shape
+    L = _lib.lib()
+    nbytes = L.pt_feature_stats_workspace_bytes(D)
+    if nbytes < 0:
+        raise _lib.PtError("pt_feature_stats: feature dimension %d is not supported" % D)
+    ws = torch.empty(nbytes // 8, dtype=torch.float64, device=feats.device)
+    mean = torch.empty(D, dtype=torch.float64, device=feats.device)
+    cov = torch.empty(D, D, dtype=torch.float64, device=feats.device)
+    _lib.check(L.pt_feature_stats(feats.data_ptr(), N, D, mean.data_ptr(), cov.data_ptr(), ws.data_ptr(), nbytes,
+                                  torch.cuda.current_stream().cuda_stream), "pt_feature_stats")
+    return mean, cov
+
+
+def frechet_distance(mu1, sigma1, mu2, sigma2, eps=1e-6):
+    """d^2 = |mu1 - mu2|^2 + Tr(S1 + S2 - 2 sqrt(S1 S2)), same steps and fallbacks as evaluation/FGD.py:190-257."""
+    from scipy import linalg
+    mu1, mu2 = np.atleast_1d(np.asarray(mu1, dtype=np.float64)), np.atleast_1d(np.asarray(mu2, dtype=np.float64))
+    sigma1, sigma2 = np.atleast_2d(np.asarray(sigma1, dtype=np.float64)), np.atleast_2d(np.asarray(sigma2, dtype=np.float64))
+    assert mu1.shape == mu2.shape and sigma1.shape == sigma2.shape
+    diff = mu1 - mu2
+    covmean = linalg.sqrtm(sigma1.dot(sigma2))
+    if isinstance(covmean, tuple):
+        covmean = covmean[0]
+    if not np.isfinite(covmean).all():
+        offset = np.eye(sigma1.shape[0]) * eps
+        covmean = linalg.sqrtm((sigma1 + offset).dot(sigma2 + offset))
+    if np.iscomplexobj(covmean):
+        if not np.allclose(np.diagonal(covmean).imag, 0, atol=1e-3):
+            raise ValueError("Imaginary component {}".format(np.max(np.abs(covmean.imag))))
+        covmean = covmean.real
+    return float(diff.dot(diff) + np.trace(sigma1) + np.trace(sigma2) - 2 * np.trace(covmean))
+
+
+class EmbeddingSpaceEvaluator:
+    """push_samples / get_scores of evaluation/FGD.py:18-188 for one feature extractor.
+
+    ``extract`` maps poses ``[n, 90, dim]`` (the layout the reference pushes, test_holisticbody.py:279) to features
+    ``[n, 128]`` on the GPU -- pass ``EmbeddingPlan(...).extract`` (engine.py)."""
+
+    def __init__(self, extract):
+        self.extract = extract
+        self.real_feat, self.gene_feat = [], []
+
+    def reset(self):
+        self.real_feat, self.gene_feat = [], []
+
+    def push_samples(self, generated_poses, real_poses):
+        # the reference's `extract` returns feat.transpose(0, 1) (embedding_net.py:150): a push contributes a [128, n] block
+        self.real_feat.append(self.extract(real_poses.float()).t().contiguous())
+        self.gene_feat.append(self.extract(generated_poses.float()).t().contiguous())
+
+    def get_scores(self):
+        """-> (frechet_dist, feat_dist) exactly as FGD.py:155-188 computes them: the stacked [128 * pushes, n] matrices are
+        handed to mean / cov with rowvar=False, i.e. statistics over feature-dimension rows with the n samples of a push
+        as columns (all pushes must have the same n <= 128); feat_dist = mean over rows of the L1 row distance."""
+        gene, real = torch.cat(self.gene_feat), torch.cat(self.real_feat)
+        gm, gs = feature_stats(gene)
+        rm, rs = feature_stats(real)
+        try:
+            fgd = frechet_distance(gm.cpu().numpy(), gs.cpu().numpy(), rm.cpu().numpy(), rs.cpu().numpy())
+        except ValueError:
+            fgd = 1e10
+        r, g = real.cpu().numpy(), gene.cpu().numpy()       # host arithmetic as in the reference (FGD.py:181-186)
+        feat_dist = float(np.mean(np.sum(np.absolute(r - g), axis=1)))
+        return fgd, feat_dist
