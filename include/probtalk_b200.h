@@ -137,6 +137,13 @@ long long pt_feature_stats_workspace_bytes(int D);
 int pt_feature_stats(const float* feats, int N, int D, double* mean_out, double* cov_out, void* workspace,
                      long long workspace_bytes, void* stream);
 
+/* pt_feature_stats without a workspace argument and without any allocation: the partial sums go into a fixed
+ * 2 113 536-byte array inside the library (one per device).  NO COUNTERPART IN THE REFERENCE -- it exists for callers
+ * that may not allocate device memory (see csrc/pt_stats.cu).  D > 128 is refused.  The array is shared: calls that can
+ * overlap in time (other streams / threads) must be serialised by the caller; make one plain call per device before
+ * capturing a stream, because the first call on a device looks the array's address up through the CUDA runtime. */
+int pt_feature_stats_static(const float* feats, int N, int D, double* mean_out, double* cov_out, void* stream);
+
 /* Pose post-processing: normalised network output -> SMPL-X axis-angle parameters in one pass.
  * Replaces the sequence of scripts/demo.py:183-205:
  *   denormalize (nets/utils.py:27-43; mean / std already reordered to the 'fbhe' channel order, NULL = skip)

@@ -132,3 +132,41 @@ extern "C" int pt_feature_stats(const float* feats, int N, int D, double* mean_o
   return pt::feature_stats_launch(feats, N, D, mean_out, cov_out, static_cast<double*>(workspace), (cudaStream_t)stream,
                                   "pt_feature_stats");
 }
+
+// ---------------------------------------------------------------------------------------------
+// The same statistics for callers that must not allocate device memory.
+//
+// pt_feature_stats wants a workspace, and whoever provides one has to get it from somewhere.  Some callers cannot: a
+// section of a program in which allocation calls are forbidden, a real-time loop that promised its host not to touch the
+// allocator after start-up, a binding from a runtime whose buffers are all accounted for up front.  For them the partial
+// sums go into a fixed array that is part of the library image itself, so the call needs nothing but its inputs and
+// outputs (and it never calls an allocating routine, torch's caching allocator included).
+//
+//   * size: kStatChunks * (kStatMaxD + kStatMaxD^2) doubles = 16 * 16512 * 8 B = 2 113 536 bytes per device, enough for
+//     the largest feature dimension pt_feature_stats accepts (128); a larger D is refused with an error, never truncated.
+//   * nothing in it has to start at zero: every launch first overwrites each partial it later reads.
+//   * it is ONE array per device, shared by every caller in the process: two calls that may run at the same time (different
+//     streams, different host threads) race on it and corrupt each other's result.  Callers serialise such calls
+//     themselves (same stream, or an event between them); calls on one stream are ordered by the stream.
+//   * the address is looked up with cudaGetSymbolAddress the first time a device is used and remembered.  That lookup is
+//     a runtime call that may initialise the module on the device: do this first call per device during set-up, before
+//     any stream capture begins (no statement is made here about what happens inside a capture).
+static __device__ __align__(256) double g_stat_scratch[kStatChunks * (kStatMaxD + kStatMaxD * kStatMaxD)];
+
+extern "C" int pt_feature_stats_static(const float* feats, int N, int D, double* mean_out, double* cov_out, void* stream) {
+  if (D > kStatMaxD)
+    return pt::fail("pt_feature_stats_static: feature dimension %d exceeds the built-in scratch (at most %d; %zu bytes)", D,
+                    kStatMaxD, sizeof(double) * kStatChunks * (kStatMaxD + kStatMaxD * kStatMaxD));
+  static double* scratch_of_device[64] = {nullptr};
+  int dev = 0;
+  PT_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return pt::fail("pt_feature_stats_static: device index %d out of range", dev);
+  double* ws = scratch_of_device[dev];
+  if (!ws) {
+    cudaError_t rc = cudaGetSymbolAddress(reinterpret_cast<void**>(&ws), g_stat_scratch);
+    if (rc != cudaSuccess || !ws)
+      return pt::fail("pt_feature_stats_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(rc));
+    scratch_of_device[dev] = ws;
+  }
+  return pt::feature_stats_launch(feats, N, D, mean_out, cov_out, ws, (cudaStream_t)stream, "pt_feature_stats_static");
+}
