@@ -220,7 +220,8 @@ def run_ours(args):
     value = world * B / (ms * 1e-3)
 
     # ---- roofline of the dominant kernel (tensor-core GEMM): per-launch device times from an event-bracketed replay
-    gemm_ms, gemm_flops, n_gemm, kinds = profile_kernels(pred, ref)
+    gemm_ms, gemm_flops, n_gemm, kinds, gemm_keys = profile_kernels(pred, ref)
+    traffic, traffic_hits = gemm_traffic(gemm_keys)
 
     # ---- end to end through the public wrapper API with host buffers
     e2e = None
@@ -246,7 +247,10 @@ def run_ours(args):
                            "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2; no flush needed"},
                 "clocks": clocks, "gpu_launches": launches_per_step * args.steps,
                 "roofline": {"bound": "tensor", "kernel": "gemm_kernel (tcgen05 bf16)", "achieved": ach, "peak": pk["tf_sust"],
-                             "unit": "TFLOP/s", "frac": ach / pk["tf_sust"], "traffic": None,
+                             "unit": "TFLOP/s", "frac": ach / pk["tf_sust"], "traffic": traffic,
+                             "traffic_source": ("DRAM read+write bytes per GEMM launch, mean over the %d of %d launches of this "
+                                                "step whose shape is in profiles/r01_ncu_gemm_suite.csv (ncu --set full)"
+                                                % (traffic_hits, n_gemm)) if traffic else None,
                              "peak_source": pk["source"] + " bf16 sustained (kernel timed inside a long step)",
                              "launches_per_step": n_gemm, "gemm_ms_per_step": gemm_ms,
                              "kernel_share_of_step": kinds},
@@ -267,15 +271,44 @@ def profile_kernels(pred, ref):
         pl.run_timed(records)
     ref.plan.run_timed(records)
     torch.cuda.synchronize()
-    totals, counts, flops = {}, {}, 0.0
-    for name, e0, e1, fl in records:
+    totals, counts, flops, keys = {}, {}, 0.0, []
+    for name, e0, e1, fl, key in records:
         totals[name] = totals.get(name, 0.0) + e0.elapsed_time(e1)
         counts[name] = counts.get(name, 0) + 1
         if name == "pt_gemm_bf16":
             flops += fl
+            keys.append(key)
     tot = sum(totals.values())
     share = {k: round(v / tot, 4) for k, v in sorted(totals.items(), key=lambda kv: -kv[1])}
-    return totals.get("pt_gemm_bf16", 0.0), flops, counts.get("pt_gemm_bf16", 0), share
+    return totals.get("pt_gemm_bf16", 0.0), flops, counts.get("pt_gemm_bf16", 0), share, keys
+
+
+def gemm_traffic(keys):
+    """DRAM bytes per GEMM launch (read + write), from the committed `ncu --set full` capture of the six transformer GEMM
+    shapes (profiles/r01_ncu_gemm_suite.csv, M = 90112; bytes scale with M for the refiner's M = 184320 launches).
+    Average over the step's launches whose shape was captured; returns (bytes_per_launch, covered_launches)."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "r01_ncu_gemm_suite.csv")
+    try:
+        rows = [r for r in csv.reader(open(path)) if r and not r[0].startswith("#")]
+        hdr = rows[0]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        cap = {}
+        for r in rows[2:]:
+            name = r[0]                              # e.g. "rn2 N512 K512 (+res,LN)", "relu N2048 K512"
+            n = int(name.split(" N")[1].split()[0]); k = int(name.split(" K")[1].split()[0])
+            rn = 2 if name.startswith("rn2") else 1 if name.startswith("rn1") else 0
+            cap[(n, k, rn)] = (float(r[ir]) + float(r[iw])) * 1e6      # ncu reports Mbyte
+    except Exception:
+        return None, 0
+    total, hit = 0.0, 0
+    for key in keys:
+        M, N, K, rn, _res = key
+        c = cap.get((N, K, rn))
+        if c is not None and M >= 90112:
+            total += c * (M / 90112.0)
+            hit += 1
+    return (total / hit, hit) if hit else (None, 0)
 
 
 def run_e2e(args, ai1, states, B, dev, world, rank):

@@ -154,7 +154,7 @@ class Plan:
                 check(rc, fn.__name__)
 
     def run_timed(self, records):
-        """Replay with a CUDA event pair around every launch; appends (name, start, end, flops) to records."""
+        """Replay with a CUDA event pair around every launch; appends (name, start, end, flops, gemm_key) to records."""
         st = _stream()
         for fn, args, flops in self.steps:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -163,7 +163,11 @@ class Plan:
             if rc != 0:
                 check(rc, fn.__name__)
             e1.record()
-            records.append((fn.__name__, e0, e1, flops))
+            key = None
+            if fn.__name__ == "pt_gemm_bf16":       # (M, N, K, row_norm, has_residual): lets a caller match launches to profiles
+                d = args[0]._obj
+                key = (d.M, d.n_valid, d.taps * d.C, d.row_norm, int(bool(d.residual)))
+            records.append((fn.__name__, e0, e1, flops, key))
 
     # -- GEMM recorders
     def gemm(self, a_t, a_rows, a_pitch, w: Weight, out_t, *, M, C_, s=1, base_row=0, rows_per_sample, t_valid,
