@@ -27,7 +27,7 @@ else:
 
 
 def run():
-    _lib.check(L.pt_attention(*args, out.data_ptr(), 512, B, 8, 64, Nq, Nk, 0.125, st))
+    _lib.check(L.pt_attention(*args, out.data_ptr(), 512, B, 8, 64, Nq, Nk, 0.125, torch.cuda.current_stream().cuda_stream))
 
 
 for _ in range(3):
@@ -42,3 +42,12 @@ torch.cuda.synchronize()
 us = e0.elapsed_time(e1) / iters * 1e3
 fl = 4.0 * B * 8 * Nq * Nk * 64
 print("attention B=%d Nq=%d Nk=%d %s: %.1f us  %.1f TFLOP/s  %.0f GB/s" % (B, Nq, Nk, mode, us, fl / us / 1e6, byts / us / 1e3))
+
+# the same launch replayed from a CUDA graph (no host cost per launch)
+g = torch.cuda.CUDAGraph()
+with torch.cuda.graph(g):
+    for _ in range(iters):
+        run()
+g.replay(); torch.cuda.synchronize()
+e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+print("   graph replay: %.1f us per launch" % (e0.elapsed_time(e1) / iters * 1e3))
