@@ -6,7 +6,7 @@ import time
 import torch
 import torch.nn.functional as F
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from oracle import probtalk_oracle as O      # noqa: E402
 from probtalk_b200 import engine as E, synthetic as S   # noqa: E402
