@@ -141,7 +141,8 @@ int pt_feature_stats(const float* feats, int N, int D, double* mean_out, double*
  * 2 113 536-byte array inside the library (one per device).  NO COUNTERPART IN THE REFERENCE -- it exists for callers
  * that may not allocate device memory (see csrc/pt_stats.cu).  D > 128 is refused.  The array is shared: calls that can
  * overlap in time (other streams / threads) must be serialised by the caller; make one plain call per device before
- * capturing a stream, because the first call on a device looks the array's address up through the CUDA runtime. */
+ * capturing a stream, because the first call on a device looks the array's address up through the CUDA runtime.
+ * The array used is the CURRENT device's: the device that owns `feats`, the outputs and `stream` must be current. */
 int pt_feature_stats_static(const float* feats, int N, int D, double* mean_out, double* cov_out, void* stream);
 
 /* Pose post-processing: normalised network output -> SMPL-X axis-angle parameters in one pass.

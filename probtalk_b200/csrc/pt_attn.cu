@@ -203,11 +203,7 @@ int launch_attn(const AttnArgs& a, int B, cudaStream_t st) {
   const int nbuf = (2 * one <= 226 * 1024) ? 2 : 1;
   const size_t smem = nbuf * one;
   if (smem > 226 * 1024) return pt::fail("pt_attention: Nq=%d Nk=%d do not fit in shared memory", a.Nq, a.Nk);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    PT_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (smem > 48 * 1024) PT_SMEM_OPT_IN(attention_kernel, smem);
   const int sms = pt::sm_count();
   int per_sm = (int)((227 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);   // __launch_bounds__(192, 2)

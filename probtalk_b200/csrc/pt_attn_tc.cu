@@ -500,13 +500,9 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
   const int grid_max = sms * per_sm;
   const int grid = n_units < grid_max ? n_units : grid_max;
   const int nch = nch_host;
-  static size_t configured[4] = {0, 0, 0, 0};
 #define PT_ATTN_LAUNCH(K)                                                                                              \
   do {                                                                                                                 \
-    if (smem > configured[K]) {                                                                                        \
-      PT_CUDA(cudaFuncSetAttribute(attention_tc_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
-      configured[K] = smem;                                                                                            \
-    }                                                                                                                  \
+    PT_SMEM_OPT_IN(attention_tc_kernel<K>, smem);                                                                      \
     attention_tc_kernel<K><<<grid, kThreadsTc, smem, st>>>(tq, tk, tv, a);                                             \
   } while (0)
   if (nch == 1) PT_ATTN_LAUNCH(1);

@@ -870,11 +870,7 @@ int make_tmap_out(CUtensorMap* tm, void* base, long long rows, long long cols, l
 
 template <int BN, int CL>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, false, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::kSmem));
-    attr_done = true;
-  }
+  PT_SMEM_OPT_IN((gemm_kernel<BN, false, CL>), Cfg<BN>::kSmem);
   const int m_super = (ka.m_tiles + CL - 1) / CL;
   const int tiles = m_super * ka.N_tiles;
   int clusters = sms / CL;
@@ -900,11 +896,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, 
 // cta_group::2 variant: pairs of CTAs, one 256-row x 256-column tile per pair step
 int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
   using Cf = Cfg<256, true>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, false, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cf::kSmem));
-    attr_done = true;
-  }
+  PT_SMEM_OPT_IN((gemm_kernel<256, false, 1, true>), Cf::kSmem);
   const int tiles = ((ka.m_tiles + 1) / 2) * ka.N_tiles;
   int pairs = sms / 2;
   if (tiles < pairs) pairs = tiles;
@@ -923,11 +915,7 @@ int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap&
 
 // row-norm variant: clusters of two CTAs, one 128-row tile per cluster step
 int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(gemm_kernel<256, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmem));
-    attr_done = true;
-  }
+  PT_SMEM_OPT_IN((gemm_kernel<256, true, 1>), Cfg<256>::kSmem);
   int clusters = sms / 2;
   if (ka.m_tiles < clusters) clusters = ka.m_tiles;
   cudaLaunchConfig_t cfg = {};

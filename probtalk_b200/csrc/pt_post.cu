@@ -99,11 +99,7 @@ extern "C" int pt_pose_postprocess(const float* poses, const float* mean, const 
   if (B > 65535) return pt::fail("pt_pose_postprocess: at most 65535 samples per call (got %d)", B);
   const size_t smem = (size_t)kTileT * (3 * n_joints + n_expr + 1) * sizeof(float);
   if (smem > 200 * 1024) return pt::fail("pt_pose_postprocess: %d joints + %d expression channels do not fit", n_joints, n_expr);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    PT_CUDA(cudaFuncSetAttribute(pose_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (smem > 48 * 1024) PT_SMEM_OPT_IN(pose_post_kernel, smem);
   pose_post_kernel<<<dim3((T + kTileT - 1) / kTileT, B), 256, smem, (cudaStream_t)stream>>>(poses, mean, stdv, lower27, out, T,
                                                                                              n_joints, n_expr);
   PT_CUDA(cudaGetLastError());

@@ -416,12 +416,8 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   a.n_tiles = (int)((rows + R - 1) / R);
   a.ctas_per_group = per_group;
   const size_t smem = sizeof(PqSmem) + 1024;
-  static bool attr_done = false;
-  if (!attr_done) {
-    PT_CUDA(cudaFuncSetAttribute(pq_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    PT_CUDA(cudaFuncSetAttribute(pq_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done = true;
-  }
+  PT_SMEM_OPT_IN(pq_search_kernel<false>, smem);
+  PT_SMEM_OPT_IN(pq_search_kernel<true>, smem);
   const unsigned grid = (unsigned)(per_group * G);
   if (score_dump) pq_search_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
   else pq_search_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);

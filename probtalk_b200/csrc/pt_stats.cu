@@ -157,16 +157,27 @@ extern "C" int pt_feature_stats_static(const float* feats, int N, int D, double*
   if (D > kStatMaxD)
     return pt::fail("pt_feature_stats_static: feature dimension %d exceeds the built-in scratch (at most %d; %zu bytes)", D,
                     kStatMaxD, sizeof(double) * kStatChunks * (kStatMaxD + kStatMaxD * kStatMaxD));
-  static double* scratch_of_device[64] = {nullptr};
+  // one cached address per device ordinal; atomics because two host threads may make the first call together (both
+  // would look up the same address, so the duplicate store is harmless)
+  static std::atomic<double*> scratch_of_device[64];
   int dev = 0;
   PT_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) return pt::fail("pt_feature_stats_static: device index %d out of range", dev);
-  double* ws = scratch_of_device[dev];
+  double* ws = scratch_of_device[dev].load(std::memory_order_acquire);
   if (!ws) {
     cudaError_t rc = cudaGetSymbolAddress(reinterpret_cast<void**>(&ws), g_stat_scratch);
     if (rc != cudaSuccess || !ws)
       return pt::fail("pt_feature_stats_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(rc));
-    scratch_of_device[dev] = ws;
+    scratch_of_device[dev].store(ws, std::memory_order_release);
+  }
+  // the array belongs to the CURRENT device: feats / outputs / stream must live there too
+  {
+    cudaPointerAttributes pa;
+    const cudaError_t qrc = cudaPointerGetAttributes(&pa, feats);
+    if (qrc != cudaSuccess) (void)cudaGetLastError();        // not a CUDA pointer: the launch below reports it
+    else if (pa.type == cudaMemoryTypeDevice && pa.device != dev)
+      return pt::fail("pt_feature_stats_static: feats live on device %d but the current device is %d (make the owning "
+                      "device current before the call)", pa.device, dev);
   }
   return pt::feature_stats_launch(feats, N, D, mean_out, cov_out, ws, (cudaStream_t)stream, "pt_feature_stats_static");
 }

@@ -73,18 +73,14 @@ class HolisticPipeline:
         self.VW = E.VQVAEWeights(vq_state, self.device)
         self.PW = E.PredictorWeights(pred_state, self.device)
         self.RW = E.RefinerWeights(ref_state, self.device)
-        self._pred, self._ref, self._dec = {}, {}, {}
+        self._pred, self._ref, self._dec = E.PlanCache(), E.PlanCache(), E.PlanCache(4)
         self.generator = None          # torch.Generator for the sampler noise (None = global CUDA RNG)
 
     def predictor(self, B, T):
-        if (B, T) not in self._pred:
-            self._pred[(B, T)] = E.PredictorPlan(self.PW, self.VW, B, T)
-        return self._pred[(B, T)]
+        return self._pred.get((B, T), lambda: E.PredictorPlan(self.PW, self.VW, B, T))
 
     def refiner(self, B, T, Tp):
-        if (B, T, Tp) not in self._ref:
-            self._ref[(B, T, Tp)] = E.RefinerPlan(self.RW, B, T, Tp)
-        return self._ref[(B, T, Tp)]
+        return self._ref.get((B, T, Tp), lambda: E.RefinerPlan(self.RW, B, T, Tp))
 
     def window(self, aud, gt, mask, labels, noise=None):
         """One All_In_One_Model('infer_on_batch') call (ai1.py:44-60) on already-batched inputs."""
@@ -120,10 +116,9 @@ class HolisticPipeline:
             input_gt[..., s:e] = p0
             input_mask[..., s:e] = 1
         codes = torch.cat([code_list[0]] + [c[:, 3:] for c in code_list[1:]], dim=1)
-        key = (B, codes.shape[1])
-        if key not in self._dec:
-            self._dec[key] = E.DecoderPlan(self.VW, B, codes.shape[1], codes=torch.zeros_like(codes))
-        prelim = F.interpolate(self._dec[key].run(codes=codes), size=t, align_corners=False, mode="linear")
+        dec = self._dec.get((B, codes.shape[1]),
+                            lambda: E.DecoderPlan(self.VW, B, codes.shape[1], codes=torch.zeros_like(codes)))
+        prelim = F.interpolate(dec.run(codes=codes), size=t, align_corners=False, mode="linear")
         input_mask.zero_()
         pred = None
         for s, e in demo_window_bounds(t, 176):

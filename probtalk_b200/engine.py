@@ -123,13 +123,42 @@ def prep_linear(w, b, device, cin_pad=None):
 class RowBuf:
     """Channels-last activation [B, Tp, C]: H zero halo rows, T valid rows, zero tail (Tp even)."""
 
-    def __init__(self, B, T, Cc, H=1, dtype=BF16, device="cuda"):
+    def __init__(self, B, T, Cc, H=1, dtype=BF16, device="cuda", even=True):
         self.B, self.T, self.C, self.H = B, T, Cc, H
-        self.Tp = _ceil(T + 2 * H, 2)
+        # an even row count lets stride-2 convolutions view the buffer as [rows / 2, 2 C]; even=False (no halo, never
+        # read with a stride) keeps exactly T rows per sample so that the buffer is a flat [B * T, C] matrix
+        self.Tp = _ceil(T + 2 * H, 2) if even else T + 2 * H
         self.t = torch.zeros(B, self.Tp, Cc, dtype=dtype, device=device)
 
     def valid(self):
         return self.t[:, self.H:self.H + self.T]
+
+
+class PlanCache:
+    """bucket key -> plan with least-recently-used eviction.  A plan owns every activation buffer of its (batch, frames)
+    bucket (gigabytes at large batches) and ragged tail windows create one bucket per length, so the caches of the
+    wrappers / driver are bounded: beyond ``capacity`` buckets the one used longest ago is dropped (its buffers and
+    CUDA graph are freed when the last reference goes)."""
+
+    def __init__(self, capacity=8):
+        from collections import OrderedDict
+        self.capacity, self._d = capacity, OrderedDict()
+
+    def get(self, key, build):
+        d = self._d
+        if key in d:
+            d.move_to_end(key)
+            return d[key]
+        plan = d[key] = build()
+        while len(d) > self.capacity:
+            d.popitem(last=False)
+        return plan
+
+    def __len__(self):
+        return len(self._d)
+
+    def __contains__(self, key):
+        return key in self._d
 
 
 class Plan:
@@ -147,11 +176,13 @@ class Plan:
         self.launches += 1
 
     def run(self):
-        st = _stream()
-        for fn, args, _ in self.steps:
-            rc = fn(*args, st)
-            if rc != 0:
-                check(rc, fn.__name__)
+        # the library configures and launches on the CURRENT device: make it the one that owns the plan's buffers
+        with torch.cuda.device(self.device):
+            st = _stream()
+            for fn, args, _ in self.steps:
+                rc = fn(*args, st)
+                if rc != 0:
+                    check(rc, fn.__name__)
 
     def run_timed(self, records):
         """Replay with a CUDA event pair around every launch; appends (name, start, end, flops, gemm_key) to records."""
@@ -769,12 +800,11 @@ class RefinerPlan:
         p = self.plan = Plan(dev)
         M = B * T
         # blank = gt*mask + interp(pred)*(1-mask)  -> rows [B*T, 384]
-        xin = RowBuf(B, T, _ceil(RW.in_dim, 64), 0, device=dev)
-        assert xin.Tp == T, "refiner windows must have an even number of frames"
+        xin = RowBuf(B, T, _ceil(RW.in_dim, 64), 0, device=dev, even=False)      # any T (odd tail windows too)
         p.call(L.pt_pack_rows, self.gt.data_ptr(), self.mask.data_ptr(), self.pred.data_ptr(), self.T_pred, xin.t.data_ptr(),
                B, RW.in_dim, T, xin.Tp, 0, xin.C, 0, 2)
         # condition = cat(audio, one_hot(mask))  -> rows [B*T, 832]
-        xc = RowBuf(B, T, _ceil(RW.aud_dim + 2, 64), 0, device=dev)
+        xc = RowBuf(B, T, _ceil(RW.aud_dim + 2, 64), 0, device=dev, even=False)
         p.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xc.t.data_ptr(), B, RW.aud_dim, T, xc.Tp, 0, xc.C, 0, 0)
         p.call(L.pt_pack_mask, self.mask.data_ptr(), xc.t.data_ptr(), B, T, xc.Tp, 0, xc.C, RW.aud_dim, 1)
         self.pe32 = RW.PE[1:T + 1].float().contiguous().to(dev)

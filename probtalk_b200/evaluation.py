@@ -56,8 +56,10 @@ def frechet_distance(mu1, sigma1, mu2, sigma2, eps=1e-6):
 class EmbeddingSpaceEvaluator:
     """push_samples / get_scores of evaluation/FGD.py:18-188 for one feature extractor.
 
-    ``extract`` maps poses ``[n, 90, dim]`` (the layout the reference pushes, test_holisticbody.py:279) to features
-    ``[n, 128]`` on the GPU -- pass ``EmbeddingPlan(...).extract`` (engine.py)."""
+    ``extract`` maps poses ``[n, dim, 90]`` (channel-first 90-frame chunks: what the reference's
+    ``transpose(1, 2).unfold(1, 90, 90).flatten(0, 1)`` produces, test_holisticbody.py:279) to features ``[n, 128]`` on the
+    GPU -- pass ``EmbeddingPlan(...).extract`` (engine.py).  ``extract`` may return a view of a buffer it reuses: the
+    features are copied here before the next call."""
 
     def __init__(self, extract):
         self.extract = extract
@@ -68,8 +70,9 @@ class EmbeddingSpaceEvaluator:
 
     def push_samples(self, generated_poses, real_poses):
         # the reference's `extract` returns feat.transpose(0, 1) (embedding_net.py:150): a push contributes a [128, n] block
-        self.real_feat.append(self.extract(real_poses.float()).t().contiguous())
-        self.gene_feat.append(self.extract(generated_poses.float()).t().contiguous())
+        # .clone(): `.t().contiguous()` of a one-chunk [1, 128] result is a no-copy view of the extractor's buffer
+        self.real_feat.append(self.extract(real_poses.float()).t().clone())
+        self.gene_feat.append(self.extract(generated_poses.float()).t().clone())
 
     def get_scores(self):
         """-> (frechet_dist, feat_dist) exactly as FGD.py:155-188 computes them: the stacked [128 * pushes, n] matrices are

@@ -120,14 +120,14 @@ class VQVAE(M.VQVAE_SC):
         self.vq_layer = pq
         self._device = torch.device(device)
         self._weights = None
-        self._plans = {}
+        self._plans = E.PlanCache()
 
     def enable_facade(self):
         pass
 
     def load_state_dict(self, sd, strict=True):
         out = super().load_state_dict(_strip(sd), strict=strict)
-        self._weights, self._plans = None, {}
+        self._weights, self._plans = None, E.PlanCache()
         return out
 
     def weights(self):
@@ -136,16 +136,14 @@ class VQVAE(M.VQVAE_SC):
         return self._weights
 
     def _plan(self, kind, *key):
-        k = (kind,) + key
-        if k not in self._plans:
+        def build():
             W = self.weights()
             if kind == "enc":
-                self._plans[k] = E.EncoderPlan(W, *key)
-            elif kind == "dec":
-                self._plans[k] = E.DecoderPlan(W, *key)
-            else:
-                self._plans[k] = E.DecoderPlan(W, *key, from_latents=True)
-        return self._plans[k]
+                return E.EncoderPlan(W, *key)
+            if kind == "dec":
+                return E.DecoderPlan(W, *key)
+            return E.DecoderPlan(W, *key, from_latents=True)
+        return self._plans.get((kind,) + key, build)
 
     def encoder(self, x):
         B, _, T = x.shape
@@ -259,7 +257,7 @@ class s2g_body_predictor(_WrapperBase):
         self.Predictor = M.PredictorNet(self.full_dim, m.code_num, 512, self.num_classes, m.groups, m.maskgit_T)
         self.VQ = self._make_vq(self.full_dim)
         self.in_dim = self.full_dim
-        self._weights, self._plans = None, {}
+        self._weights, self._plans = None, E.PlanCache()
         self.noise_generator = None
 
     def state_dict(self):
@@ -271,15 +269,13 @@ class s2g_body_predictor(_WrapperBase):
         for name in ("AudEnc", "Predictor", "TextEnc"):
             if name in sd:
                 getattr(self, name).load_state_dict(sd[name])
-        self._weights, self._plans = None, {}
+        self._weights, self._plans = None, E.PlanCache()
 
     def _plan(self, B, T):
         if self._weights is None:
             self._weights = E.PredictorWeights({"AudEnc": self.AudEnc.state_dict(), "Predictor": self.Predictor.state_dict()},
                                                self.device)
-        if (B, T) not in self._plans:
-            self._plans[(B, T)] = E.PredictorPlan(self._weights, self.VQ.weights(), B, T, self.Predictor.T)
-        return self._plans[(B, T)]
+        return self._plans.get((B, T), lambda: E.PredictorPlan(self._weights, self.VQ.weights(), B, T, self.Predictor.T))
 
     def _infer(self, aud, id, B, gt_poses, mask, noise=None):
         assert self.args.infer, "train mode"
@@ -316,7 +312,7 @@ class s2g_body_refiner(_WrapperBase):
         self.AudEnc = torch.nn.Identity()
         self.VQ = self._make_vq(self.full_dim)      # kept for checkpoint/API parity; inference never uses it (refiner.py:84-90)
         self.in_dim = self.vq_dim = self.full_dim
-        self._weights, self._plans = None, {}
+        self._weights, self._plans = None, E.PlanCache()
 
     def state_dict(self):
         return {"HFTransformer": self.RTransformer.state_dict(), "AudEnc": self.AudEnc.state_dict(), "generator_optim": None}
@@ -324,14 +320,12 @@ class s2g_body_refiner(_WrapperBase):
     def load_state_dict(self, state_dict):
         if state_dict.get("HFTransformer") is not None:
             self.RTransformer.load_state_dict(_strip(state_dict["HFTransformer"]))
-        self._weights, self._plans = None, {}
+        self._weights, self._plans = None, E.PlanCache()
 
     def _plan(self, B, T, Tp):
         if self._weights is None:
             self._weights = E.RefinerWeights({"HFTransformer": self.RTransformer.state_dict()}, self.device)
-        if (B, T, Tp) not in self._plans:
-            self._plans[(B, T, Tp)] = E.RefinerPlan(self._weights, B, T, Tp)
-        return self._plans[(B, T, Tp)]
+        return self._plans.get((B, T, Tp), lambda: E.RefinerPlan(self._weights, B, T, Tp))
 
     def infer_on_batch(self, aud, B=1, id=0, gt_poses=None, mask=None, pred_poses=None, **kw):
         assert self.args.infer, "train mode"

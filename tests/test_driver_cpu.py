@@ -46,8 +46,17 @@ def test_demo_window_bounds():
     assert len(w) == 12 and w[-1] == (1650, 1800)
     w = D.demo_window_bounds(1800, 176)
     assert len(w) == 13 and w[-1] == (1752, 1800)
-    for s, e in w:
-        assert (e - s) % 2 == 0                     # refiner buckets need an even number of frames
+    # odd utterance lengths give odd tail windows (RefinerPlan takes any number of frames)
+    assert D.demo_window_bounds(1801, 176)[-1] == (1752, 1801)
+    assert D.eval_window_bounds(331)[-1] == (330, 331)
+
+
+def test_plan_cache_is_lru_bounded():
+    from probtalk_b200 import engine as E
+    c, built = E.PlanCache(capacity=2), []
+    for k in ("a", "b", "a", "c", "b"):
+        c.get(k, lambda k=k: built.append(k) or k)
+    assert built == ["a", "b", "c", "b"] and len(c) == 2 and "a" not in c
 
 
 def _free_port():
