@@ -52,6 +52,17 @@ int pt_pq_gather(const void* idx, int idx_is_i64, const float* codebooks, void* 
                  long long os_b, long long os_c, long long os_w, int B, int W, int G, int K, int D, int* bad_count,
                  void* stream);
 
+/* Codebook gather fused into the decoder's first convolution.  Replaces quantize_all (nets/spg/vqvae_modules.py:557-564)
+ * followed by DecoderSC.aft_vq_conv, the 1x1 Conv1d(G*D -> N) at nets/inpainting/vqvae_1d_sc.py:259-261:
+ *   out[b, w, n] = bias[n] + sum_g table[g][idx[b, w, g]][n],   table[g] = C_g . W[:, g*D:(g+1)*D]^T  (fp32 [G, K, N],
+ *   prepared once per checkpoint by the caller), fp32 sums in group order.
+ *   idx [B, W, G] int64 / int32;  out bf16 at out[b*oss + w*ors + n] (N multiple of 8, 16-byte aligned rows);
+ *   out_lo: NULL, or the lo plane of a split-bf16 pair (see pt_gemm_desc.split);
+ *   bad_count int32 [1] or NULL: incremented for every index outside [0, K) (such entries read code 0). */
+int pt_pq_gather_conv1x1(const void* idx, int idx_is_i64, const float* table, const float* bias, void* out_bf16,
+                         void* out_lo, long long oss, long long ors, int B, int W, int G, int K, int N, int* bad_count,
+                         void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Tensor-core contraction engine (TMA + tcgen05/TMEM).  One descriptor covers the dense ops of
  *   ConvNormRelu / Res_CNR_Stack (BN folded)    nets/spg/vqvae_modules.py:107-245
@@ -96,6 +107,17 @@ typedef struct pt_gemm_desc {
   int label_rows;
   int norm_classes;       /* rows of norm_a / norm_b that labels may select: 1..4 when labels is not NULL (the tables are
                            * staged on chip; labels are clamped to the range) */
+  /* split-bf16 ("bf16x3") arithmetic, the tolerance-tight mode (fp32 reference: every nn.Conv1d / nn.Linear above).
+   * An fp32 value v travels as two bf16 planes  hi = bf16(v), lo = bf16(v - hi)  (16 mantissa bits).  split != 0:
+   *   A    = the plane pair (a, a_lo), same rows / pitch;
+   *   W    = [N, 2*taps*C]: each row is its hi plane followed by its lo plane;
+   *   acc  = A_hi W_hi + A_hi W_lo + A_lo W_hi  (three tensor-core passes, fp32 accumulation);
+   *   bf16 outputs are written as the pair (out, out_lo), bf16 residuals are read as (residual, residual_lo);
+   *   fp32 outputs / residuals are unchanged; row_norm is not available. */
+  int split;
+  const void* a_lo;
+  void* out_lo;
+  const void* residual_lo;
 } pt_gemm_desc;
 
 int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);
@@ -112,6 +134,13 @@ int pt_attention(const void* q, long long q_stride, const void* k, long long k_s
                  long long v_stride, void* out, long long out_stride, int B, int heads, int head_dim, int Nq, int Nk,
                  float scale, void* stream);
 
+/* The same attention core for the split-bf16 (tolerance-tight) mode: q, k, v fp32 (same row / head addressing, strides in
+ * elements), fp32 CUDA-core arithmetic, softmax normalised before P.V like the reference; the output is bf16, or a
+ * split-bf16 pair when out_lo is not NULL.  head_dim 64, 1 <= Nk <= 256. */
+int pt_attention_f32(const float* q, long long q_stride, const float* k, long long k_stride, const float* v,
+                     long long v_stride, void* out_bf16, void* out_lo, long long out_stride, int B, int heads,
+                     int head_dim, int Nq, int Nk, float scale, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Layout kernels between the reference's channel-first fp32 tensors [B, C, T] and the engine's
  * channels-last bf16 rows [B, Tp, Cp] (H zero halo rows in front of every sample).
@@ -119,10 +148,11 @@ int pt_attention(const void* q, long long q_stride, const void* k, long long k_s
  *   mode 0: src                     (audio features, predictor.py:428 / refiner.py:544)
  *   mode 1: src * mask              (input_poses = gt_poses * mask, predictor.py:425)
  *   mode 2: src * mask + interp(pred, T) * (1 - mask)     (refiner.py:524-529, linear F.interpolate)
+ * dst_lo: NULL, or the lo plane of a split-bf16 pair (same layout as dst_bf16; see pt_gemm_desc.split).
  * pt_pack_mask writes the mask channel (onehot = 0; predictornet.py:85) or the two one-hot channels
  * (onehot = 1; RTransformer.py:218). */
-int pt_pack_rows(const float* src, const float* mask, const float* pred, int pred_T, void* dst_bf16, int B, int C,
-                 int T, int Tp, int H, int Cp, int c_off, int mode, void* stream);
+int pt_pack_rows(const float* src, const float* mask, const float* pred, int pred_T, void* dst_bf16, void* dst_lo, int B,
+                 int C, int T, int Tp, int H, int Cp, int c_off, int mode, void* stream);
 int pt_pack_mask(const float* mask, void* dst_bf16, int B, int T, int Tp, int H, int Cp, int c_off, int onehot,
                  void* stream);
 
@@ -145,6 +175,15 @@ int pt_feature_stats(const float* feats, int N, int D, double* mean_out, double*
  * The array used is the CURRENT device's: the device that owns `feats`, the outputs and `stream` must be current. */
 int pt_feature_stats_static(const float* feats, int N, int D, double* mean_out, double* cov_out, void* stream);
 
+/* Motion metrics of the evaluator, fp64 results, deterministic, no scratch beyond the outputs.
+ * pt_lvd: landmark velocity difference, LVD -> Batch_LVD with symmetrical = False, weight = False
+ *   (evaluation/metrics.py:79-94, :26-77; called at scripts/test_holisticbody.py:120,130):
+ *   gt [T, J, D], pr [B, T, J, D] fp32 -> per_sample [B] = sum_t sum_j | |d pr|_2 - |d gt|_2 | / (T - 1), mean_out [1].
+ * pt_diversity: mean pairwise L1 distance between samples (evaluation/metrics.py:96-110):
+ *   kps [B, L] fp32 -> per_pair [B (B - 1) / 2] (pairs i < j, i outer) = mean_l |x_i - x_j|, mean_out [1]. */
+int pt_lvd(const float* gt, const float* pr, int B, int T, int J, int D, double* per_sample, double* mean_out, void* stream);
+int pt_diversity(const float* kps, int B, long long L, double* per_pair, double* mean_out, void* stream);
+
 /* Pose post-processing: normalised network output -> SMPL-X axis-angle parameters in one pass.
  * Replaces the sequence of scripts/demo.py:183-205:
  *   denormalize (nets/utils.py:27-43; mean / std already reordered to the 'fbhe' channel order, NULL = skip)
@@ -161,20 +200,20 @@ int pt_interp_blend(const float* known, const float* mask, const float* pred, in
 
 /* out = LayerNorm512(in + residual), eps 1e-5: the `x = norm_i(x + sublayer(x))` of the post-norm layer
  * (PTransformer.py:329-331).  in fp32 or bf16, residual bf16 or NULL (may alias out_bf16), fp32 statistics,
- * fp32 and/or bf16 out. */
-int pt_layernorm512(const void* in, int in_f32, const void* residual_bf16, const float* gamma, const float* beta,
-                    float* out_f32, void* out_bf16, int M, void* stream);
+ * fp32 and/or bf16 out.  residual_lo / out_lo: NULL, or the lo planes of split-bf16 pairs (pt_gemm_desc.split). */
+int pt_layernorm512(const void* in, int in_f32, const void* residual_bf16, const void* residual_lo, const float* gamma,
+                    const float* beta, float* out_f32, void* out_bf16, void* out_lo, int M, void* stream);
 
 /* StylizationBlock_V3 'sb' branch before its output Linear (PTransformer.py:134-139):
  *   out = SiLU( LN(in) * (1 + scale) + shift ),  [scale | shift] = mod[labels[row / rows_per_sample]]  (mod: [n_classes, 1024] fp32,
  *   the emb_layers_2 Linear applied to SiLU(class_embed) -- precomputed per class by the host). */
 int pt_ln_mod_silu512(const void* in, int in_f32, const float* gamma, const float* beta, const float* mod,
-                      const int* labels, int rows_per_sample, void* out_bf16, int M, void* stream);
+                      const int* labels, int rows_per_sample, void* out_bf16, void* out_lo, int M, void* stream);
 
 /* Token embedding + positional encodings (PTransformer.py:659-679): row r -> float32(emb[tokens[r]] + pe64[r % N]),
  * the fp64 add + fp32 round of the reference.  bad_count (or NULL) counts tokens outside [0, n_emb). */
 int pt_embed_tokens512(const int* tokens, const float* emb, int n_emb, const double* pe64, int N, float* out_f32,
-                       void* out_bf16, int M, int* bad_count, void* stream);
+                       void* out_bf16, void* out_lo, int M, int* bad_count, void* stream);
 
 /* One MaskGIT refinement step: PTransformer.sample_good loop body (PTransformer.py:603-638) and
  * mask_by_random_topk (:696-704).  logits fp32 [B, N, n_codes]; cur_ids/next_ids int32 [B, N] (may alias);

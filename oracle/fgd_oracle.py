@@ -68,3 +68,30 @@ def scores(gene_batches, real_batches):
     fgd = frechet_distance(gm, gs, rm, rs)
     feat_dist = float(np.mean(np.sum(np.absolute(real - gene), axis=1)))
     return fgd, feat_dist
+
+
+def lvd(gt_kps, pr_kps):
+    """LVD of evaluation/metrics.py:79-94 for gt [T, J, D] and pr [B, T, J, D] (torch tensors): the Batch_LVD branch
+    (:26-77) with symmetrical = False, weight = False, which is how the evaluator calls it
+    (scripts/test_holisticbody.py:120,130)."""
+    import torch
+    gt_kps, pr_kps = gt_kps.squeeze(), pr_kps.squeeze()
+    if pr_kps.dim() == 3:
+        gt_v = (gt_kps[1:] - gt_kps[:-1]).norm(p=2, dim=-1)
+        pr_v = (pr_kps[1:] - pr_kps[:-1]).norm(p=2, dim=-1)
+        return float((pr_v - gt_v).abs().sum(dim=-1).mean())
+    length = min(gt_kps.shape[0], pr_kps.shape[1])
+    gt_kps, pr_kps = gt_kps[:length], pr_kps[:, :length]
+    gt_v = (gt_kps[1:] - gt_kps[:-1]).norm(p=2, dim=-1)
+    pr_v = (pr_kps[:, 1:] - pr_kps[:, :-1]).norm(p=2, dim=-1)
+    w = 1 / gt_v.shape[0]
+    return float(((pr_v - gt_v).abs().sum(dim=-1) * w).sum(dim=-1).mean())
+
+
+def diversity(kps):
+    """diversity of evaluation/metrics.py:96-110: kps [bs, seq, dim] (numpy), mean over pairs of mean |x_i - x_j|."""
+    dis = []
+    for i in range(kps.shape[0]):
+        for j in range(i + 1, kps.shape[0]):
+            dis.append(np.mean(np.abs(kps[i] - kps[j])))
+    return float(np.mean(dis))

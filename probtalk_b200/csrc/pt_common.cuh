@@ -261,4 +261,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// split-bf16 pair of two fp32 values: hi = bf16(v), lo = bf16(v - hi)  (hi + lo carries 16 mantissa bits of v)
+__device__ __forceinline__ void split_bf16x2(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(v0, v1);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = pack_bf16x2(v0 - __low2float(h), v1 - __high2float(h));
+}
+
 }  // namespace pt

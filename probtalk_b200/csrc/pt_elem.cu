@@ -30,6 +30,7 @@ struct PackArgs {
   const float* src; const float* mask; const float* pred;
   __nv_bfloat16* dst;
   int B, C, T, Tp, H, Cp, c_off, mode, Tpred;
+  __nv_bfloat16* dst_lo;        // split arithmetic: the lo plane (same layout as dst) or null
 };
 
 __global__ void pack_rows_kernel(PackArgs a) {
@@ -52,8 +53,12 @@ __global__ void pack_rows_kernel(PackArgs a) {
   __syncthreads();
   for (int i = ty; i < 32; i += 8) {
     const int t = t0 + i, c = c0 + tx;
-    if (t < a.T && c < a.C)
-      a.dst[((size_t)b * a.Tp + a.H + t) * a.Cp + a.c_off + c] = __float2bfloat16_rn(tile[tx][i]);
+    if (t < a.T && c < a.C) {
+      const size_t o = ((size_t)b * a.Tp + a.H + t) * a.Cp + a.c_off + c;
+      const __nv_bfloat16 h = __float2bfloat16_rn(tile[tx][i]);
+      a.dst[o] = h;
+      if (a.dst_lo) a.dst_lo[o] = __float2bfloat16_rn(tile[tx][i] - __bfloat162float(h));
+    }
   }
 }
 
@@ -118,18 +123,24 @@ __global__ void __launch_bounds__(256, 5) pack_rows_slab_kernel(PackArgs a) {
   __syncthreads();
   const int cg = (tid & 7) * 4;                        // 4 consecutive channels of the slab
   for (int t = tid >> 3; t < a.T; t += 32) {
-    __nv_bfloat16* d = a.dst + ((size_t)b * a.Tp + a.H + t) * a.Cp + a.c_off + c0 + cg;
+    const size_t off = ((size_t)b * a.Tp + a.H + t) * a.Cp + a.c_off + c0 + cg;
+    __nv_bfloat16* d = a.dst + off;
     const float v0 = slab[(cg + 0) * ld + t], v1 = slab[(cg + 1) * ld + t];
     const float v2 = slab[(cg + 2) * ld + t], v3 = slab[(cg + 3) * ld + t];
+    uint2 hi, lo;
+    pt::split_bf16x2(v0, v1, hi.x, lo.x);
+    pt::split_bf16x2(v2, v3, hi.y, lo.y);
     if (c0 + cg + 3 < a.C && ((reinterpret_cast<uintptr_t>(d) & 7) == 0)) {
-      uint2 pk;
-      pk.x = pt::pack_bf16x2(v0, v1); pk.y = pt::pack_bf16x2(v2, v3);
-      *reinterpret_cast<uint2*>(d) = pk;
+      *reinterpret_cast<uint2*>(d) = hi;
+      if (a.dst_lo) *reinterpret_cast<uint2*>(a.dst_lo + off) = lo;
     } else {
-      if (c0 + cg + 0 < a.C) d[0] = __float2bfloat16_rn(v0);
-      if (c0 + cg + 1 < a.C) d[1] = __float2bfloat16_rn(v1);
-      if (c0 + cg + 2 < a.C) d[2] = __float2bfloat16_rn(v2);
-      if (c0 + cg + 3 < a.C) d[3] = __float2bfloat16_rn(v3);
+      const uint32_t h4[2] = {hi.x, hi.y}, l4[2] = {lo.x, lo.y};
+      for (int j = 0; j < 4; ++j) {
+        if (c0 + cg + j < a.C) {
+          reinterpret_cast<uint16_t*>(d)[j] = (uint16_t)(h4[j >> 1] >> (16 * (j & 1)));
+          if (a.dst_lo) reinterpret_cast<uint16_t*>(a.dst_lo + off)[j] = (uint16_t)(l4[j >> 1] >> (16 * (j & 1)));
+        }
+      }
     }
   }
 }
@@ -265,8 +276,10 @@ __device__ __forceinline__ void ln_stats(const float (&v)[16], float& mean, floa
 // nn.LayerNorm (norm1/2/3 of DeepSupervisionLayer, PTransformer.py:329-331): fp32 in -> fp32 and/or bf16 out
 template <typename InT>
 __global__ void ln_kernel(const InT* __restrict__ in, const __nv_bfloat16* __restrict__ res,
+                          const __nv_bfloat16* __restrict__ res_lo,
                           const float* __restrict__ gamma, const float* __restrict__ beta,
-                          float* __restrict__ out32, __nv_bfloat16* __restrict__ out16, int M) {
+                          float* __restrict__ out32, __nv_bfloat16* __restrict__ out16, __nv_bfloat16* __restrict__ out16_lo,
+                          int M) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -277,6 +290,11 @@ __global__ void ln_kernel(const InT* __restrict__ in, const __nv_bfloat16* __res
     load_row16(res + (size_t)row * kDModel, lane, r);
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] += r[i];
+    if (res_lo) {                              // split residual: the lo plane carries the next 8 mantissa bits
+      load_row16(res_lo + (size_t)row * kDModel, lane, r);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] += r[i];
+    }
   }
   float mean, rstd;
   ln_stats(v, mean, rstd);
@@ -287,7 +305,13 @@ __global__ void ln_kernel(const InT* __restrict__ in, const __nv_bfloat16* __res
     const float y0 = (v[4 * i] - mean) * rstd * g.x + bb.x, y1 = (v[4 * i + 1] - mean) * rstd * g.y + bb.y;
     const float y2 = (v[4 * i + 2] - mean) * rstd * g.z + bb.z, y3 = (v[4 * i + 3] - mean) * rstd * g.w + bb.w;
     if (out32) *reinterpret_cast<float4*>(out32 + (size_t)row * kDModel + c) = make_float4(y0, y1, y2, y3);
-    if (out16) *reinterpret_cast<uint2*>(out16 + (size_t)row * kDModel + c) = make_uint2(pt::pack_bf16x2(y0, y1), pt::pack_bf16x2(y2, y3));
+    if (out16) {
+      uint2 hi, lo;
+      pt::split_bf16x2(y0, y1, hi.x, lo.x);
+      pt::split_bf16x2(y2, y3, hi.y, lo.y);
+      *reinterpret_cast<uint2*>(out16 + (size_t)row * kDModel + c) = hi;
+      if (out16_lo) *reinterpret_cast<uint2*>(out16_lo + (size_t)row * kDModel + c) = lo;
+    }
   }
 }
 
@@ -297,7 +321,7 @@ template <typename InT>
 __global__ void ln_mod_silu_kernel(const InT* __restrict__ in, const float* __restrict__ gamma,
                                    const float* __restrict__ beta, const float* __restrict__ mod,
                                    const int* __restrict__ labels, int rows_per_sample,
-                                   __nv_bfloat16* __restrict__ out, int M) {
+                                   __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo, int M) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -319,14 +343,19 @@ __global__ void ln_mod_silu_kernel(const InT* __restrict__ in, const float* __re
       const float u = y[j] * (1.f + s4[j]) + h4[j];
       y[j] = u / (1.f + __expf(-u));
     }
-    *reinterpret_cast<uint2*>(out + (size_t)row * kDModel + c) = make_uint2(pt::pack_bf16x2(y[0], y[1]), pt::pack_bf16x2(y[2], y[3]));
+    uint2 hi, lo;
+    pt::split_bf16x2(y[0], y[1], hi.x, lo.x);
+    pt::split_bf16x2(y[2], y[3], hi.y, lo.y);
+    *reinterpret_cast<uint2*>(out + (size_t)row * kDModel + c) = hi;
+    if (out_lo) *reinterpret_cast<uint2*>(out_lo + (size_t)row * kDModel + c) = lo;
   }
 }
 
 // tok_emb lookup + positional encodings (PTransformer.py:659-679): x = float32( emb[tok] + pe64[n] ), n = row % N
 __global__ void embed_tokens_kernel(const int* __restrict__ tokens, const float* __restrict__ emb,
                                     const double* __restrict__ pe64, float* __restrict__ out32,
-                                    __nv_bfloat16* __restrict__ out16, int M, int N, int n_emb, int* bad) {
+                                    __nv_bfloat16* __restrict__ out16, __nv_bfloat16* __restrict__ out16_lo, int M, int N,
+                                    int n_emb, int* bad) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -342,7 +371,13 @@ __global__ void embed_tokens_kernel(const int* __restrict__ tokens, const float*
     const float y0 = (float)((double)x.x + p0.x), y1 = (float)((double)x.y + p0.y);
     const float y2 = (float)((double)x.z + p1.x), y3 = (float)((double)x.w + p1.y);
     if (out32) *reinterpret_cast<float4*>(out32 + (size_t)row * kDModel + c) = make_float4(y0, y1, y2, y3);
-    if (out16) *reinterpret_cast<uint2*>(out16 + (size_t)row * kDModel + c) = make_uint2(pt::pack_bf16x2(y0, y1), pt::pack_bf16x2(y2, y3));
+    if (out16) {
+      uint2 hi, lo;
+      pt::split_bf16x2(y0, y1, hi.x, lo.x);
+      pt::split_bf16x2(y2, y3, hi.y, lo.y);
+      *reinterpret_cast<uint2*>(out16 + (size_t)row * kDModel + c) = hi;
+      if (out16_lo) *reinterpret_cast<uint2*>(out16_lo + (size_t)row * kDModel + c) = lo;
+    }
   }
 }
 
@@ -417,15 +452,15 @@ __global__ void __launch_bounds__(128) maskgit_step_kernel(const float* __restri
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ C ABI
-extern "C" int pt_pack_rows(const float* src, const float* mask, const float* pred, int pred_T, void* dst_bf16, int B,
-                            int C, int T, int Tp, int H, int Cp, int c_off, int mode, void* stream) {
+extern "C" int pt_pack_rows(const float* src, const float* mask, const float* pred, int pred_T, void* dst_bf16,
+                            void* dst_lo, int B, int C, int T, int Tp, int H, int Cp, int c_off, int mode, void* stream) {
   if (B <= 0 || C <= 0 || T <= 0) return 0;
   if (!src || !dst_bf16) return pt::fail("pt_pack_rows: null pointer");
   if (mode < 0 || mode > 2) return pt::fail("pt_pack_rows: bad mode %d", mode);
   if (mode >= 1 && !mask) return pt::fail("pt_pack_rows: mode %d needs a mask", mode);
   if (mode == 2 && (!pred || pred_T <= 0)) return pt::fail("pt_pack_rows: mode 2 needs pred");
   if (c_off + C > Cp || H + T > Tp) return pt::fail("pt_pack_rows: destination too small");
-  PackArgs a{src, mask, pred, (__nv_bfloat16*)dst_bf16, B, C, T, Tp, H, Cp, c_off, mode, pred_T};
+  PackArgs a{src, mask, pred, (__nv_bfloat16*)dst_bf16, B, C, T, Tp, H, Cp, c_off, mode, pred_T, (__nv_bfloat16*)dst_lo};
   if (T <= kPackMaxT && B <= 65535) {
     const size_t smem = (size_t)32 * (T + 1) * sizeof(float);   // <= 48 KB
     if (T <= 192) pack_rows_slab_kernel<6><<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
@@ -473,40 +508,43 @@ extern "C" int pt_interp_blend(const float* known, const float* mask, const floa
   return 0;
 }
 
-extern "C" int pt_layernorm512(const void* in, int in_f32, const void* residual_bf16, const float* gamma,
-                               const float* beta, float* out_f32, void* out_bf16, int M, void* stream) {
+extern "C" int pt_layernorm512(const void* in, int in_f32, const void* residual_bf16, const void* residual_lo,
+                               const float* gamma, const float* beta, float* out_f32, void* out_bf16, void* out_lo, int M,
+                               void* stream) {
   if (M <= 0) return 0;
   if (!in || !gamma || !beta || (!out_f32 && !out_bf16)) return pt::fail("pt_layernorm512: null pointer");
+  if ((residual_lo && !residual_bf16) || (out_lo && !out_bf16)) return pt::fail("pt_layernorm512: a lo plane needs its hi plane");
   const __nv_bfloat16* res = (const __nv_bfloat16*)residual_bf16;
+  const __nv_bfloat16* rlo = (const __nv_bfloat16*)residual_lo;
   if (in_f32)
-    ln_kernel<float><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const float*)in, res, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
+    ln_kernel<float><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const float*)in, res, rlo, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M);
   else
-    ln_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, res, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, M);
+    ln_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, res, rlo, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M);
   PT_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int pt_ln_mod_silu512(const void* in, int in_f32, const float* gamma, const float* beta, const float* mod,
-                                 const int* labels, int rows_per_sample, void* out_bf16, int M, void* stream) {
+                                 const int* labels, int rows_per_sample, void* out_bf16, void* out_lo, int M, void* stream) {
   if (M <= 0) return 0;
   if (!in || !gamma || !beta || !mod || !labels || !out_bf16) return pt::fail("pt_ln_mod_silu512: null pointer");
   if (rows_per_sample <= 0) return pt::fail("pt_ln_mod_silu512: rows_per_sample must be positive");
   cudaStream_t st = (cudaStream_t)stream;
   if (in_f32)
-    ln_mod_silu_kernel<float><<<(M + 7) / 8, 256, 0, st>>>((const float*)in, gamma, beta, mod, labels, rows_per_sample, (__nv_bfloat16*)out_bf16, M);
+    ln_mod_silu_kernel<float><<<(M + 7) / 8, 256, 0, st>>>((const float*)in, gamma, beta, mod, labels, rows_per_sample, (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M);
   else
-    ln_mod_silu_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, st>>>((const __nv_bfloat16*)in, gamma, beta, mod, labels, rows_per_sample, (__nv_bfloat16*)out_bf16, M);
+    ln_mod_silu_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, st>>>((const __nv_bfloat16*)in, gamma, beta, mod, labels, rows_per_sample, (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M);
   PT_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int pt_embed_tokens512(const int* tokens, const float* emb, int n_emb, const double* pe64, int N,
-                                  float* out_f32, void* out_bf16, int M, int* bad_count, void* stream) {
+                                  float* out_f32, void* out_bf16, void* out_lo, int M, int* bad_count, void* stream) {
   if (M <= 0) return 0;
   if (!tokens || !emb || !pe64 || (!out_f32 && !out_bf16)) return pt::fail("pt_embed_tokens512: null pointer");
   if (N <= 0) return pt::fail("pt_embed_tokens512: N must be positive");
   embed_tokens_kernel<<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>(tokens, emb, pe64, out_f32, (__nv_bfloat16*)out_bf16,
-                                                                    M, N, n_emb, bad_count);
+                                                                    (__nv_bfloat16*)out_lo, M, N, n_emb, bad_count);
   PT_CUDA(cudaGetLastError());
   return 0;
 }

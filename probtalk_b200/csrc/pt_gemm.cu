@@ -72,6 +72,12 @@ struct GemmKernelArgs {
   int norm_classes;
   int res_mma;                    // row-norm: the bf16 residual tile is added by the tensor core (identity x residual), tmap_r
   int tma_store;                  // tmap_o describes the output as a dense bf16 [M, n_valid] matrix: 32 x 32 boxes are stored by TMA
+  // split-bf16 ("bf16x3") arithmetic: the K loop runs three passes  A_hi W_hi + A_hi W_lo + A_lo W_hi  (tmap_r = the lo
+  // plane of A, W rows are [hi | lo]); bf16 outputs / residuals are hi + lo plane pairs
+  int split;
+  int k_base;                     // K blocks of ONE pass = taps * (C / 64)
+  void* out_lo;
+  const void* residual_lo;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act, float slope) {
@@ -185,7 +191,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     pt::tma_prefetch_desc(&tmap_a);
     pt::tma_prefetch_desc(&tmap_b);
     if (p.tma_store) pt::tma_prefetch_desc(&tmap_o);
-    if (p.res_mma) pt::tma_prefetch_desc(&tmap_r);
+    if (p.res_mma || p.split) pt::tma_prefetch_desc(&tmap_r);
   }
   if (warp == 1 && lane == 0) {
     const uint32_t full_count = (kRowNorm && p.res_mma) ? 2u : 1u;
@@ -271,25 +277,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
         const int m0 = tile_m0(tile), n0 = tile_n0(tile);
         for (int kk = 0; kk < p.K_iters; ++kk) {
-          const int tap = kk / p.c_iters, cc = kk - tap * p.c_iters;
+          // split arithmetic: pass 0 = A_hi W_hi, pass 1 = A_hi W_lo (weight columns shifted by one K extent),
+          // pass 2 = A_lo W_hi (A read through the lo plane's tensor map)
+          int pass = 0, kq = kk;
+          if (p.split) { pass = kk / p.k_base; kq = kk - pass * p.k_base; }
+          const int tap = kq / p.c_iters, cc = kq - tap * p.c_iters;
+          const int wcol = (pass == 1 ? kq + p.k_base : kq) * BK;
+          const CUtensorMap* tma = (pass == 2) ? &tmap_r : &tmap_a;
           pt::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
           if constexpr (k2) {
             // both CTAs' boxes complete on the leader's barrier: the leader arms it for the pair's bytes
             if (rank == 0) pt::mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
-            pt::tma_load_2d_2sm(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
-            pt::tma_load_2d_2sm(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0 + (int)rank * (BN / 2));
+            pt::tma_load_2d_2sm(sa, tma, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
+            pt::tma_load_2d_2sm(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0 + (int)rank * (BN / 2));
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
             continue;
           }
           pt::mbar_expect_tx(&full[stage], C::kStageBytes);
-          pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
+          pt::tma_load_2d(sa, tma, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
           if constexpr (kCL == 1) {
-            pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
+            pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0);
           } else {
             // this CTA's slice of the weight box (BN / kCL rows), delivered to every CTA of the cluster
             constexpr int kSliceRows = BN / kCL;
-            pt::tma_load_2d_mc(sa + C::kABytes + rank * (kSliceRows * 128), &tmap_b, &full[stage], kk * BK,
+            pt::tma_load_2d_mc(sa + C::kABytes + rank * (kSliceRows * 128), &tmap_b, &full[stage], wcol,
                                n0 + (int)rank * kSliceRows, kMcMask);
           }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -369,7 +381,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     const bool gate = (p.act == PT_ACT_GATE);
     // the common case (bf16 row-major output, no residual, identity / ReLU) gets a lean path: with K = 512 the
     // epilogue of a 128 x 256 tile has only ~4000 cycles before it starts to stall the tensor core
-    const bool lean = row_major && !p.out_f32 && !p.residual && !kRowNorm &&
+    const bool lean = row_major && !p.out_f32 && !p.residual && !kRowNorm && !p.split &&
                       (p.act == PT_ACT_NONE || p.act == PT_ACT_RELU);
     const bool lean_relu = (p.act == PT_ACT_RELU);
     const int pr = lane >> 2, pc = lane & 3;             // piece mapping: row pr + 8*j, 16-byte piece pc
@@ -712,25 +724,30 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
               }
             }
           } else {
-            __syncwarp();
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int rr = pr + 8 * j;
-              uint4 x = make_uint4(0, 0, 0, 0);
-              if (ro4[j] >= 0 && n + pc * 8 < p.n_valid)
-                x = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rs4[j] + n) + pc);
-              *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(rr, pc)) = x;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const uint4 x = *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(lane, i));
-              const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+            // bf16 residual; in split arithmetic it is a (hi, lo) plane pair and both planes are added
+            const int planes = p.split ? 2 : 1;
+            for (int pl = 0; pl < planes; ++pl) {
+              const __nv_bfloat16* rp = static_cast<const __nv_bfloat16*>(pl ? p.residual_lo : p.residual);
+              __syncwarp();
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&w4[j]);
-                f[8 * i + 2 * j] += __bfloat162float(hh.x);
-                f[8 * i + 2 * j + 1] += __bfloat162float(hh.y);
+                const int rr = pr + 8 * j;
+                uint4 x = make_uint4(0, 0, 0, 0);
+                if (ro4[j] >= 0 && n + pc * 8 < p.n_valid)
+                  x = __ldg(reinterpret_cast<const uint4*>(rp + rs4[j] + n) + pc);
+                *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(rr, pc)) = x;
+              }
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 x = *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(lane, i));
+                const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&w4[j]);
+                  f[8 * i + 2 * j] += __bfloat162float(hh.x);
+                  f[8 * i + 2 * j + 1] += __bfloat162float(hh.y);
+                }
               }
             }
           }
@@ -738,24 +755,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         // ---- activation + store through the tile
         if (gate) {
           // interleaved columns (a0,b0,a1,b1,...) -> tanh(a) * sigmoid(b): 16 bf16 outputs (32 B) per row
-          uint32_t g8[8];
+          float g[16];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float g0 = tanhf(f[4 * i]) * (1.f / (1.f + __expf(-f[4 * i + 1])));
-            const float g1 = tanhf(f[4 * i + 2]) * (1.f / (1.f + __expf(-f[4 * i + 3])));
-            g8[i] = pt::pack_bf16x2(g0, g1);
-          }
-          __syncwarp();
-          *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, 0)) = make_uint4(g8[0], g8[1], g8[2], g8[3]);
-          *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, 1)) = make_uint4(g8[4], g8[5], g8[6], g8[7]);
-          __syncwarp();
+          for (int i = 0; i < 16; ++i) g[i] = tanhf(f[2 * i]) * (1.f / (1.f + __expf(-f[2 * i + 1])));
+          const int planes = p.split ? 2 : 1;
+          for (int pl = 0; pl < planes; ++pl) {
+            __nv_bfloat16* outp = static_cast<__nv_bfloat16*>(pl ? p.out_lo : p.out);
+            uint32_t g8[8];
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            const int rr = (lane >> 1) + 16 * j, pp = lane & 1;
-            const long long ro = row_out[rr];
-            if (ro >= 0)
-              *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + (n >> 1) + pp * 8) =
-                  *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pp));
+            for (int i = 0; i < 8; ++i) g8[i] = pt::pack_bf16x2(g[2 * i], g[2 * i + 1]);
+            __syncwarp();
+            *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, 0)) = make_uint4(g8[0], g8[1], g8[2], g8[3]);
+            *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, 1)) = make_uint4(g8[4], g8[5], g8[6], g8[7]);
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const int rr = (lane >> 1) + 16 * j, pp = lane & 1;
+              const long long ro = row_out[rr];
+              if (ro >= 0)
+                *reinterpret_cast<uint4*>(outp + ro + (n >> 1) + pp * 8) =
+                    *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pp));
+            }
+            if (planes == 2 && pl == 0) {                   // what the hi plane could not represent goes to the lo plane
+#pragma unroll
+              for (int i = 0; i < 16; ++i) g[i] -= __bfloat162float(__float2bfloat16_rn(g[i]));
+            }
           }
         } else if (p.out_f32) {
 #pragma unroll
@@ -777,22 +801,29 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             }
           }
         } else {
-          __syncwarp();
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, i)) = make_uint4(
-                pt::pack_bf16x2(apply_act(f[8 * i], p.act, p.slope), apply_act(f[8 * i + 1], p.act, p.slope)),
-                pt::pack_bf16x2(apply_act(f[8 * i + 2], p.act, p.slope), apply_act(f[8 * i + 3], p.act, p.slope)),
-                pt::pack_bf16x2(apply_act(f[8 * i + 4], p.act, p.slope), apply_act(f[8 * i + 5], p.act, p.slope)),
-                pt::pack_bf16x2(apply_act(f[8 * i + 6], p.act, p.slope), apply_act(f[8 * i + 7], p.act, p.slope)));
-          __syncwarp();
+          for (int i = 0; i < 32; ++i) f[i] = apply_act(f[i], p.act, p.slope);
+          const int planes = p.split ? 2 : 1;
+          for (int pl = 0; pl < planes; ++pl) {
+            __nv_bfloat16* outp = static_cast<__nv_bfloat16*>(pl ? p.out_lo : p.out);
+            __syncwarp();
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int rr = pr + 8 * j;
-            const long long ro = ro4[j];
-            if (ro >= 0 && n + pc * 8 < p.n_valid)
-              *(reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + ro + n) + pc) =
-                  *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pc));
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(tile + PT_TILE_OFF(lane, i)) = make_uint4(
+                  pt::pack_bf16x2(f[8 * i], f[8 * i + 1]), pt::pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
+                  pt::pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pt::pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int rr = pr + 8 * j;
+              const long long ro = ro4[j];
+              if (ro >= 0 && n + pc * 8 < p.n_valid)
+                *(reinterpret_cast<uint4*>(outp + ro + n) + pc) = *reinterpret_cast<const uint4*>(tile + PT_TILE_OFF(rr, pc));
+            }
+            if (planes == 2 && pl == 0) {                   // lo plane = what the hi plane could not represent
+#pragma unroll
+              for (int i = 0; i < 32; ++i) f[i] -= __bfloat162float(__float2bfloat16_rn(f[i]));
+            }
           }
         }
       }
@@ -967,6 +998,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   // A viewed as [a_rows / s, s * C] (tap j of a stride-2 conv = row j/2, column half j%2)
   if (d->a_rows % d->s) return pt::fail("pt_gemm_bf16: a_rows (%lld) not divisible by stride", d->a_rows);
   if (make_tmap(&ta, d->a, d->a_rows / d->s, (long long)d->s * d->C, (long long)d->s * d->a_pitch, BM)) return 1;
+  if (d->split) {
+    if (d->row_norm) return pt::fail("pt_gemm_bf16: split arithmetic has no row_norm epilogue");
+    if (!d->a_lo || (reinterpret_cast<uintptr_t>(d->a_lo) & 15)) return pt::fail("pt_gemm_bf16: split needs a 16-byte aligned a_lo plane");
+    if (!d->out_f32 && (!d->out_lo || d->ocs != 1 || (reinterpret_cast<uintptr_t>(d->out_lo) & 15)))
+      return pt::fail("pt_gemm_bf16: split with a bf16 output needs a row-major, 16-byte aligned out_lo plane");
+    if (d->residual && !d->res_f32 && (!d->residual_lo || (reinterpret_cast<uintptr_t>(d->residual_lo) & 15)))
+      return pt::fail("pt_gemm_bf16: split with a bf16 residual needs a 16-byte aligned residual_lo plane");
+  }
   if (d->row_norm) {
     if (d->row_norm < 1 || d->row_norm > 2) return pt::fail("pt_gemm_bf16: bad row_norm %d", d->row_norm);
     if (d->N != 512 || d->n_valid != 512 || d->ocs != 1 || d->out_f32 || (d->residual && d->res_f32) || d->act != PT_ACT_NONE)
@@ -1007,10 +1046,14 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     two_cta = !off && !d->row_norm && BN == 256 && CL == 1 &&
               ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= 2LL * sms;
   }
-  if (make_tmap(&tb, d->w, d->N, (long long)d->taps * d->C, (long long)d->taps * d->C, two_cta ? 128 : BN / CL)) return 1;
+  // split arithmetic: weight rows are [hi (taps*C) | lo (taps*C)]
+  const long long wcols = (long long)(d->split ? 2 : 1) * d->taps * d->C;
+  if (make_tmap(&tb, d->w, d->N, wcols, wcols, two_cta ? 128 : BN / CL)) return 1;
 
   GemmKernelArgs ka;
-  ka.M = d->M; ka.N_tiles = d->N / BN; ka.c_iters = d->C / BK; ka.K_iters = d->taps * ka.c_iters;
+  ka.M = d->M; ka.N_tiles = d->N / BN; ka.c_iters = d->C / BK; ka.k_base = d->taps * ka.c_iters;
+  ka.split = d->split ? 1 : 0; ka.K_iters = (ka.split ? 3 : 1) * ka.k_base;
+  ka.out_lo = d->out_lo; ka.residual_lo = d->residual_lo;
   ka.C = d->C; ka.s = d->s; ka.base_row = d->base_row;
   ka.rows_per_sample = d->rows_per_sample; ka.t_valid = d->t_valid; ka.n_valid = d->n_valid;
   ka.oss = d->oss; ka.ors = d->ors; ka.ocs = d->ocs; ka.rss = d->rss; ka.rrs = d->rrs;
@@ -1028,7 +1071,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
                        (d->M <= d->rows_per_sample || d->oss == (long long)d->rows_per_sample * d->ors) &&
                        d->ors >= d->n_valid && (d->ors % 8) == 0 &&
                        (d->n_valid % 8) == 0 && (reinterpret_cast<uintptr_t>(d->out) & 15) == 0;
-    if (!off && dense) {
+    if (!off && dense && !d->split) {
       if (make_tmap_out(&to, d->out, d->M, d->n_valid, d->ors)) return 1;
       ka.tma_store = 1;
     }
@@ -1046,6 +1089,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
       ka.res_mma = 1;
     }
   }
+  if (d->split && make_tmap(&tr, d->a_lo, d->a_rows / d->s, (long long)d->s * d->C, (long long)d->s * d->a_pitch, BM)) return 1;
   if (d->row_norm) return launch_rownorm(ta, tb, to, tr, ka, sms, st);
   if (two_cta) return launch_2cta(ta, tb, to, tr, ka, sms, st);
   if (BN == 128) return launch<128, 1>(ta, tb, to, tr, ka, sms, st);

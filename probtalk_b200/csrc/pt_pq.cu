@@ -384,7 +384,71 @@ __global__ void pq_gather_kernel(const IdxT* __restrict__ idx, const float* __re
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// gather fused into the decoder's first (1x1) convolution.  aft_vq_conv is linear and its input is a concatenation of
+// G codebook rows, so
+//     out[r, n] = b[n] + sum_c W[n, c] e[r, c] = b[n] + sum_g T_g[idx[r, g]][n],   T_g = C_g . W[:, gD:(g+1)D]^T
+// with the G tables (G x K x N fp32, 2 MB for vq.json: L2 resident) computed once per checkpoint.  No quantized
+// tensor, no GEMM: G table rows are read per output row and one bf16 row (or a split-bf16 pair) is written.
+// One thread = 8 consecutive output columns of one row (a 16-byte store); N / 8 threads cover a row.
+template <typename IdxT>
+__global__ void __launch_bounds__(256) pq_gather_conv_kernel(const IdxT* __restrict__ idx, const float* __restrict__ table,
+                                                              const float* __restrict__ bias,
+                                                              __nv_bfloat16* __restrict__ out_hi,
+                                                              __nv_bfloat16* __restrict__ out_lo, long long oss,
+                                                              long long ors, long long rows, int W, int G, int K, int N,
+                                                              int* bad) {
+  const int per_row = N >> 3;
+  const long long total = rows * per_row;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / per_row;
+    const int n = (int)(i - row * per_row) << 3;
+    float acc[8];
+    {
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + n)), b1 = __ldg(reinterpret_cast<const float4*>(bias + n) + 1);
+      acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
+    }
+    for (int g = 0; g < G; ++g) {
+      long long j = (long long)idx[row * G + g];
+      if (j < 0 || j >= K) { if (bad && n == 0) atomicAdd(bad, 1); j = 0; }
+      const float4* t = reinterpret_cast<const float4*>(table + ((size_t)g * K + j) * N + n);
+      const float4 t0 = __ldg(t), t1 = __ldg(t + 1);
+      acc[0] += t0.x; acc[1] += t0.y; acc[2] += t0.z; acc[3] += t0.w; acc[4] += t1.x; acc[5] += t1.y; acc[6] += t1.z; acc[7] += t1.w;
+    }
+    uint4 hi, lo;
+    pt::split_bf16x2(acc[0], acc[1], hi.x, lo.x); pt::split_bf16x2(acc[2], acc[3], hi.y, lo.y);
+    pt::split_bf16x2(acc[4], acc[5], hi.z, lo.z); pt::split_bf16x2(acc[6], acc[7], hi.w, lo.w);
+    const long long b = row / W, w = row - b * W;
+    const long long off = b * oss + w * ors + n;
+    *reinterpret_cast<uint4*>(out_hi + off) = hi;
+    if (out_lo) *reinterpret_cast<uint4*>(out_lo + off) = lo;
+  }
+}
+
 }  // namespace
+
+extern "C" int pt_pq_gather_conv1x1(const void* idx, int idx_is_i64, const float* table, const float* bias, void* out_bf16,
+                                    void* out_lo, long long oss, long long ors, int B, int W, int G, int K, int N,
+                                    int* bad_count, void* stream) {
+  const long long rows = (long long)B * W;
+  if (rows <= 0) return 0;
+  if (!idx || !table || !bias || !out_bf16) return pt::fail("pt_pq_gather_conv1x1: null pointer");
+  if (G < 1 || K < 1 || N < 8 || (N & 7)) return pt::fail("pt_pq_gather_conv1x1: need G, K >= 1 and N a multiple of 8 (got %d, %d, %d)", G, K, N);
+  if (((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(bias) | reinterpret_cast<uintptr_t>(out_bf16) |
+        reinterpret_cast<uintptr_t>(out_lo)) & 15) || (oss & 7) || (ors & 7))
+    return pt::fail("pt_pq_gather_conv1x1: table, bias, outputs and output strides must be 16-byte aligned");
+  const long long total = rows * (N >> 3);
+  const int blocks = (int)min((long long)pt::sm_count() * 8, (total + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (idx_is_i64)
+    pq_gather_conv_kernel<long long><<<blocks, 256, 0, st>>>((const long long*)idx, table, bias, (__nv_bfloat16*)out_bf16,
+                                                             (__nv_bfloat16*)out_lo, oss, ors, rows, W, G, K, N, bad_count);
+  else
+    pq_gather_conv_kernel<int><<<blocks, 256, 0, st>>>((const int*)idx, table, bias, (__nv_bfloat16*)out_bf16,
+                                                       (__nv_bfloat16*)out_lo, oss, ors, rows, W, G, K, N, bad_count);
+  PT_CUDA(cudaGetLastError());
+  return 0;
+}
 
 extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long long zs_w, int B, int W, int G,
                             int K, int D, const float* codebooks, long long* idx_out, float* gap_out,

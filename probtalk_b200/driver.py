@@ -68,11 +68,12 @@ def demo_window_bounds(t: int, length: int, cover: int = 30):
 class HolisticPipeline:
     """predictor + refiner + PQ-VAE over fixed weights; plans are cached per (batch, frames) bucket."""
 
-    def __init__(self, vq_state, pred_state, ref_state, device="cuda"):
+    def __init__(self, vq_state, pred_state, ref_state, device="cuda", precision="bf16"):
         self.device = torch.device(device)
-        self.VW = E.VQVAEWeights(vq_state, self.device)
-        self.PW = E.PredictorWeights(pred_state, self.device)
-        self.RW = E.RefinerWeights(ref_state, self.device)
+        self.precision = precision
+        self.VW = E.VQVAEWeights(vq_state, self.device, precision=precision)
+        self.PW = E.PredictorWeights(pred_state, self.device, precision)
+        self.RW = E.RefinerWeights(ref_state, self.device, precision)
         self._pred, self._ref, self._dec = E.PlanCache(), E.PlanCache(), E.PlanCache(4)
         self.generator = None          # torch.Generator for the sampler noise (None = global CUDA RNG)
 
@@ -82,36 +83,43 @@ class HolisticPipeline:
     def refiner(self, B, T, Tp):
         return self._ref.get((B, T, Tp), lambda: E.RefinerPlan(self.RW, B, T, Tp))
 
-    def window(self, aud, gt, mask, labels, noise=None):
+    def window(self, aud, gt, mask, labels, noise=None, force_codes=None):
         """One All_In_One_Model('infer_on_batch') call (ai1.py:44-60) on already-batched inputs."""
         B, _, T = aud.shape
-        poses, codes = self.predictor(B, T).run(aud, gt, mask, labels, noise=noise, generator=self.generator)
+        poses, codes = self.predictor(B, T).run(aud, gt, mask, labels, noise=noise, generator=self.generator,
+                                                force_codes=force_codes)
         out = self.refiner(B, T, T).run(aud, gt, mask, poses, labels)
         return out, codes
 
-    def windows_eval(self, aud, gt, mask, labels):
-        """aud [B,768,t], gt [B,376,t], mask [B,1,t] -> poses [B,376,t]  (test_holisticbody.py:239-262)."""
+    def windows_eval(self, aud, gt, mask, labels, noise=None, force_codes=None, return_codes=False):
+        """aud [B,768,t], gt [B,376,t], mask [B,1,t] -> poses [B,376,t]  (test_holisticbody.py:239-262).
+        noise / force_codes: optional lists with one entry per window ((u, gumbel) to inject / codes to teacher-force)."""
         input_gt, input_mask = gt.clone(), mask.clone()
-        pred = None
-        for s, e in eval_window_bounds(aud.shape[-1]):
-            p0, _ = self.window(aud[..., s:e].contiguous(), input_gt[..., s:e].contiguous(),
-                                input_mask[..., s:e].contiguous(), labels)
+        pred, used = None, []
+        for w, (s, e) in enumerate(eval_window_bounds(aud.shape[-1])):
+            p0, cd = self.window(aud[..., s:e].contiguous(), input_gt[..., s:e].contiguous(),
+                                 input_mask[..., s:e].contiguous(), labels, noise=None if noise is None else noise[w],
+                                 force_codes=None if force_codes is None else force_codes[w])
+            used.append(cd.clone())
             pred = p0.clone() if pred is None else torch.cat([pred, p0[..., 30:]], -1)
             input_gt[..., s:e] = p0
             input_mask[..., s:e] = 1
-        return gt * mask + pred * (1 - mask)
+        out = gt * mask + pred * (1 - mask)
+        return (out, used) if return_codes else out
 
-    def windows_demo(self, aud, labels):
+    def windows_demo(self, aud, labels, noise=None, force_codes=None):
         """aud [B,768,t] -> poses [B,376,t]  (scripts/demo.py:116-181, generalised to any t)."""
         B, _, t = aud.shape
         dev = self.device
         input_gt = torch.zeros(B, self.PW.mot_dim, t, device=dev)
         input_mask = torch.zeros(B, 1, t, device=dev)
         code_list = []
-        for s, e in demo_window_bounds(t, 180):
+        for w, (s, e) in enumerate(demo_window_bounds(t, 180)):
             plan = self.predictor(B, e - s)
             p0, codes = plan.run(aud[..., s:e].contiguous(), input_gt[..., s:e].contiguous(),
-                                 input_mask[..., s:e].contiguous(), labels, generator=self.generator)
+                                 input_mask[..., s:e].contiguous(), labels, generator=self.generator,
+                                 noise=None if noise is None else noise[w],
+                                 force_codes=None if force_codes is None else force_codes[w])
             code_list.append(codes.clone())
             input_gt[..., s:e] = p0
             input_mask[..., s:e] = 1

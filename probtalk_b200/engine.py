@@ -46,16 +46,18 @@ def _bn_scale_shift(sd, prefix, eps=1e-5):
 
 
 class Weight:
-    """bf16 [Npad, taps*Cp] matrix + fp32 bias [Npad] on the device."""
+    """bf16 [Npad, taps*Cp] matrix + fp32 bias [Npad] on the device.  split=True: the matrix is [Npad, 2*taps*Cp], every
+    row its hi plane followed by its lo plane (w = hi + lo to 16 mantissa bits), for the split-bf16 arithmetic mode."""
 
-    def __init__(self, mat, bias, taps, Cp, n_valid, cin=None):
+    def __init__(self, mat, bias, taps, Cp, n_valid, cin=None, split=False):
         self.mat, self.bias, self.taps, self.Cp, self.n_valid = mat, bias, taps, Cp, n_valid
         self.N = mat.shape[0]
         self.cin = cin if cin is not None else Cp       # true (unpadded) input channels per tap
+        self.split = split
 
 
-def _finish(wm, bias, taps, Cp, device):
-    """wm fp32 [N, taps, Cin] -> padded bf16 matrix."""
+def _finish(wm, bias, taps, Cp, device, split=False):
+    """wm fp32 [N, taps, Cin] -> padded bf16 matrix (or the [hi | lo] pair of matrices)."""
     N, _, Cin = wm.shape
     Npad = _ceil(N, 128)
     full = torch.zeros(Npad, taps, Cp, dtype=F32, device=wm.device)
@@ -63,10 +65,17 @@ def _finish(wm, bias, taps, Cp, device):
     b = torch.zeros(Npad, dtype=F32, device=wm.device)
     if bias is not None:
         b[:N] = bias
-    return Weight(full.reshape(Npad, taps * Cp).to(device=device, dtype=BF16).contiguous(), b.to(device), taps, Cp, N, Cin)
+    full = full.reshape(Npad, taps * Cp)
+    hi = full.to(BF16)
+    if split:
+        lo = (full - hi.float()).to(BF16)
+        mat = torch.cat([hi, lo], dim=1)
+    else:
+        mat = hi
+    return Weight(mat.to(device).contiguous(), b.to(device), taps, Cp, N, Cin, split)
 
 
-def prep_conv(w, b, device, bn=None, extra=None, gate=False, cin_pad=None):
+def prep_conv(w, b, device, bn=None, extra=None, gate=False, cin_pad=None, split=False):
     """Conv1d weight [Cout, Cin, k] (+ folded BatchNorm (scale, shift), + a same-geometry residual
     conv (w_res, b_res) summed in) -> tap-major matrix W[n, j*Cp + c] = w[n, c, j].
     gate=True interleaves the two halves of the output channels (a0, b0, a1, b1, ...)."""
@@ -84,10 +93,10 @@ def prep_conv(w, b, device, bn=None, extra=None, gate=False, cin_pad=None):
         w = torch.stack([w[:h], w[h:]], dim=1).reshape(Cout, Cin, k)
         b = torch.stack([b[:h], b[h:]], dim=1).reshape(Cout)
     Cp = cin_pad or _ceil(Cin, 64)
-    return _finish(w.permute(0, 2, 1).contiguous(), b, k, Cp, device)
+    return _finish(w.permute(0, 2, 1).contiguous(), b, k, Cp, device, split)
 
 
-def prep_convT(w, b, device, bn=None, extra=None):
+def prep_convT(w, b, device, bn=None, extra=None, split=False):
     """ConvTranspose1d k4 s2 p1 weight [Cin, Cout, 4] -> two phase matrices (even / odd outputs):
     out[2t]   = x[t-1] W[:,:,3] + x[t] W[:,:,1],   out[2t+1] = x[t] W[:,:,2] + x[t+1] W[:,:,0]."""
     w, b = w.float(), b.float()
@@ -104,16 +113,16 @@ def prep_convT(w, b, device, bn=None, extra=None):
     phases = []
     for taps in ((3, 1), (2, 0)):
         wm = torch.stack([w[:, :, taps[0]].t(), w[:, :, taps[1]].t()], dim=1)     # [Cout, 2, Cin]
-        phases.append(_finish(wm.contiguous(), b, 2, Cp, device))
+        phases.append(_finish(wm.contiguous(), b, 2, Cp, device, split))
     return phases
 
 
-def prep_linear(w, b, device, cin_pad=None):
+def prep_linear(w, b, device, cin_pad=None, split=False):
     """nn.Linear / 1x1 conv weight [out, in] (or [out, in, 1])."""
     if w.dim() == 3:
         w = w[:, :, 0]
     Cp = cin_pad or _ceil(w.shape[1], 64)
-    return _finish(w.float().unsqueeze(1).contiguous(), None if b is None else b.float(), 1, Cp, device)
+    return _finish(w.float().unsqueeze(1).contiguous(), None if b is None else b.float(), 1, Cp, device, split)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -123,15 +132,55 @@ def prep_linear(w, b, device, cin_pad=None):
 class RowBuf:
     """Channels-last activation [B, Tp, C]: H zero halo rows, T valid rows, zero tail (Tp even)."""
 
-    def __init__(self, B, T, Cc, H=1, dtype=BF16, device="cuda", even=True):
+    def __init__(self, B, T, Cc, H=1, dtype=BF16, device="cuda", even=True, split=False):
         self.B, self.T, self.C, self.H = B, T, Cc, H
         # an even row count lets stride-2 convolutions view the buffer as [rows / 2, 2 C]; even=False (no halo, never
         # read with a stride) keeps exactly T rows per sample so that the buffer is a flat [B * T, C] matrix
         self.Tp = _ceil(T + 2 * H, 2) if even else T + 2 * H
-        self.t = torch.zeros(B, self.Tp, Cc, dtype=dtype, device=device)
+        # split (tolerance-tight mode): two bf16 planes, value = hi + lo
+        split = split and dtype == BF16
+        self.planes = torch.zeros(2 if split else 1, B, self.Tp, Cc, dtype=dtype, device=device)
+        self.t = self.planes[0]
+        self.lo = self.planes[1] if split else None
 
     def valid(self):
         return self.t[:, self.H:self.H + self.T]
+
+    def load_f32(self, x):
+        """Set the valid rows from an fp32 tensor [B, T, C] (test / bring-up hook; the lo plane gets x - bf16(x))."""
+        hi = x.to(self.t.dtype)
+        self.valid().copy_(hi)
+        if self.lo is not None:
+            self.lo[:, self.H:self.H + self.T].copy_((x.float() - hi.float()).to(self.lo.dtype))
+
+    def valid_f32(self):
+        """The valid rows as fp32 (hi + lo for a split buffer)."""
+        v = self.valid().float()
+        return v if self.lo is None else v + self.lo[:, self.H:self.H + self.T].float()
+
+
+class Mat:
+    """Flat activation matrix [rows, C]: bf16, a split-bf16 (hi, lo) pair, or fp32 (lo = None)."""
+
+    def __init__(self, rows, Cc, device, split=False, dtype=BF16):
+        split = split and dtype == BF16
+        self.planes = torch.zeros(2 if split else 1, rows, Cc, dtype=dtype, device=device)
+        self.t = self.planes[0]
+        self.lo = self.planes[1] if split else None
+
+    def f32(self):
+        return self.t.float() if self.lo is None else self.t.float() + self.lo.float()
+
+
+def _planes(x):
+    """(hi / only plane, lo plane or None) of a tensor, Mat or RowBuf."""
+    if x is None or torch.is_tensor(x):
+        return x, None
+    return x.t, x.lo
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
 
 
 class PlanCache:
@@ -203,9 +252,20 @@ class Plan:
     # -- GEMM recorders
     def gemm(self, a_t, a_rows, a_pitch, w: Weight, out_t, *, M, C_, s=1, base_row=0, rows_per_sample, t_valid,
              oss, ors, ocs=1, out_off=0, act=ACT_NONE, slope=0.2, residual=None, rss=0, rrs=0, res_off=0, a_off=0,
-             n_valid=None, use_bias=True, row_norm=0, norm_a=None, norm_b=None, labels=None, label_rows=1):
+             n_valid=None, use_bias=True, row_norm=0, norm_a=None, norm_b=None, labels=None, label_rows=1,
+             a_lo=None, out_lo=None, residual_lo=None):
         d = GemmDesc()
         d.a = a_t.data_ptr() + 2 * a_off
+        if w.split:
+            # split-bf16 arithmetic: every bf16 operand / result is a (hi, lo) plane pair
+            assert a_lo is not None and row_norm == 0, "a split weight needs a split A operand"
+            assert out_t.dtype == F32 or out_lo is not None
+            assert residual is None or residual.dtype == F32 or residual_lo is not None
+            d.split = 1
+            d.a_lo = a_lo.data_ptr() + 2 * a_off
+            d.out_lo = out_lo.data_ptr() + 2 * out_off if (out_lo is not None and out_t.dtype != F32) else None
+            d.residual_lo = residual_lo.data_ptr() + 2 * res_off if (residual_lo is not None and residual.dtype != F32) else None
+        # (a bf16 weight reads only the hi plane of a split operand)
         d.a_rows, d.a_pitch = a_rows, a_pitch
         d.w = w.mat.data_ptr()
         assert C_ == w.Cp, (C_, w.Cp)
@@ -228,7 +288,7 @@ class Plan:
         d.norm_b = norm_b.data_ptr() if norm_b is not None else None
         d.norm_classes = (norm_a.numel() // 512) if norm_a is not None else 0
         d.labels = labels.data_ptr() if labels is not None else None
-        self.keep += [a_t, w, out_t, residual, d, norm_a, norm_b, labels]
+        self.keep += [a_t, w, out_t, residual, d, norm_a, norm_b, labels, a_lo, out_lo, residual_lo]
         # algorithmic FLOPs: real output rows x real output channels x real input channels (no padding / halo credit)
         flops = 2.0 * M * (t_valid / float(rows_per_sample)) * d.n_valid * w.taps * w.cin
         self.call(_lib.lib().pt_gemm_bf16, C.byref(d), flops=flops)
@@ -251,10 +311,11 @@ class Plan:
         kw = {}
         if residual is not None:
             assert residual.T == out.T and residual.C == n_out
-            kw = dict(residual=residual.t, rss=residual.Tp * residual.C, rrs=residual.C, res_off=residual.H * residual.C)
+            kw = dict(residual=residual.t, rss=residual.Tp * residual.C, rrs=residual.C, res_off=residual.H * residual.C,
+                      residual_lo=residual.lo)
         self.gemm(x.t, x.B * x.Tp, x.C, w, out.t, M=M, C_=x.C, s=stride, base_row=base, rows_per_sample=rps,
                   t_valid=out.T, oss=out.Tp * out.C, ors=out.C, out_off=out.H * out.C + out_c_off, act=act, slope=slope,
-                  **kw)
+                  a_lo=x.lo, out_lo=out.lo, **kw)
 
     def convT(self, x: RowBuf, phases, out: RowBuf, *, act=ACT_NONE, slope=0.2):
         """ConvTranspose1d k4 s2 p1 as two phase GEMMs (even / odd output rows)."""
@@ -263,59 +324,91 @@ class Plan:
             assert w.Cp == x.C
             self.gemm(x.t, x.B * x.Tp, x.C, w, out.t, M=x.B * x.Tp, C_=x.C, s=1, base_row=x.H - 1 + ph,
                       rows_per_sample=x.Tp, t_valid=x.T, oss=out.Tp * out.C, ors=2 * out.C,
-                      out_off=(out.H + ph) * out.C, act=act, slope=slope)
+                      out_off=(out.H + ph) * out.C, act=act, slope=slope, a_lo=x.lo, out_lo=out.lo)
 
-    def linear(self, a_t, M, w: Weight, out_t, *, out_cols=None, act=ACT_NONE, residual=None, rss=0, rrs=0,
+    def linear(self, a, M, w: Weight, out, *, out_cols=None, act=ACT_NONE, residual=None, rss=0, rrs=0,
                rows_per_sample=None, out_off=0, a_pitch=None, a_off=0, **norm):
-        """Plain row-major GEMM: out[m, :] = act(a[m, :] @ W^T + b (+ residual))."""
+        """Plain row-major GEMM: out[m, :] = act(a[m, :] @ W^T + b (+ residual)).
+        a / out / residual: tensors, or Mat / RowBuf objects (whose lo planes ride along in split arithmetic)."""
+        a_t, a_lo = _planes(a)
+        out_t, out_lo = _planes(out)
+        res_t, res_lo = _planes(residual)
         ors = out_cols if out_cols is not None else w.n_valid
         rps = rows_per_sample or max(M, 1)
         self.gemm(a_t, M, a_pitch or w.Cp, w, out_t, M=M, C_=w.Cp, rows_per_sample=rps, t_valid=rps,
-                  oss=rps * ors, ors=ors, out_off=out_off, act=act, residual=residual, rss=rss, rrs=rrs, a_off=a_off, **norm)
+                  oss=rps * ors, ors=ors, out_off=out_off, act=act, residual=res_t, rss=rss, rrs=rrs, a_off=a_off,
+                  a_lo=a_lo if w.split else None, out_lo=out_lo, residual_lo=res_lo, **norm)
 
 
 # ----------------------------------------------------------------------------------------------
 # PQ-VAE  (reference: nets/inpainting/vqvae_1d_sc.py:197-324, nets/spg/vqvae_modules.py:107-245)
 # ----------------------------------------------------------------------------------------------
 
-class VQVAEWeights:
-    """Folded weights of VQVAE_SC(376, 512, 128, num_hiddens=1024, num_residual_layers=2)."""
+PRECISIONS = ("bf16", "bf16x3")
 
-    def __init__(self, sd, device, groups=4):
+
+def _check_precision(precision):
+    if precision not in PRECISIONS:
+        raise ValueError("precision must be one of %s (got %r)" % (PRECISIONS, precision))
+    return precision == "bf16x3"
+
+
+class VQVAEWeights:
+    """Folded weights of VQVAE_SC(376, 512, 128, num_hiddens=1024, num_residual_layers=2).
+
+    The ENCODER is always prepared for split-bf16 arithmetic (A_hi W_hi + A_hi W_lo + A_lo W_hi, fp32-grade): its
+    output z feeds a nearest-code search, where a bf16-sized error flips indices, and it is not on the throughput path.
+    The decoder follows ``precision`` ("bf16" or "bf16x3")."""
+
+    def __init__(self, sd, device, groups=4, precision="bf16"):
         dev = device
         sd = {k: v.to(dev) for k, v in sd.items() if torch.is_tensor(v)}
         self.device = dev
+        self.precision = precision
+        self.precise = _check_precision(precision)
 
-        def cnr(p, sample="none"):
+        def cnr(p, sample, split):
             bn = _bn_scale_shift(sd, p + ".norm")
             if sample == "none":
-                return prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, bn=bn)
+                return prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, bn=bn, split=split)
             ex = (sd[p + ".residual_layer.weight"], sd[p + ".residual_layer.bias"])
             if sample == "down":
-                return prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, bn=bn, extra=ex)
-            return prep_convT(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, bn=bn, extra=ex)
+                return prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, bn=bn, extra=ex, split=split)
+            return prep_convT(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, bn=bn, extra=ex, split=split)
 
-        def stack(p):
-            return [cnr(p + "._layers.0"), cnr(p + "._layers.1"), cnr(p)]      # last: conv + norm of the stack itself
+        def stack(p, split):        # last: conv + norm of the stack itself
+            return [cnr(p + "._layers.0", "none", split), cnr(p + "._layers.1", "none", split), cnr(p, "none", split)]
 
-        self.enc_project = cnr("encoder.project")
-        self.enc_stacks = [stack("encoder._enc_%d" % i) for i in (1, 2, 3, 4)]
-        self.enc_downs = [cnr("encoder._down_%d" % i, "down") for i in (1, 2, 3)]
-        self.pre_vq = prep_linear(sd["encoder.pre_vq_conv.weight"], sd["encoder.pre_vq_conv.bias"], dev)
-        self.aft_vq = prep_linear(sd["decoder.aft_vq_conv.weight"], sd["decoder.aft_vq_conv.bias"], dev)
-        self.dec_stacks = [stack("decoder._dec_%d" % i) for i in (1, 2, 3, 4)]
-        self.dec_ups = [cnr("decoder._up_%d" % i, "up") for i in (2, 3, 4)]
-        self.dec_project = prep_linear(sd["decoder.project.weight"], sd["decoder.project.bias"], dev)
+        ds = self.precise
+        self.enc_project = cnr("encoder.project", "none", True)
+        self.enc_stacks = [stack("encoder._enc_%d" % i, True) for i in (1, 2, 3, 4)]
+        self.enc_downs = [cnr("encoder._down_%d" % i, "down", True) for i in (1, 2, 3)]
+        self.pre_vq = prep_linear(sd["encoder.pre_vq_conv.weight"], sd["encoder.pre_vq_conv.bias"], dev, split=True)
+        self.aft_vq = prep_linear(sd["decoder.aft_vq_conv.weight"], sd["decoder.aft_vq_conv.bias"], dev, split=ds)
+        self.dec_stacks = [stack("decoder._dec_%d" % i, ds) for i in (1, 2, 3, 4)]
+        self.dec_ups = [cnr("decoder._up_%d" % i, "up", ds) for i in (2, 3, 4)]
+        self.dec_project = prep_linear(sd["decoder.project.weight"], sd["decoder.project.bias"], dev, split=ds)
         self.codebooks = torch.stack([sd["vq_layer.embeddings_%d" % g].float() for g in range(groups)]).contiguous()
         self.groups = groups
+        self.n_codes, self.code_dim = self.codebooks.shape[1], self.codebooks.shape[2]
         self.in_dim = sd["encoder.project.conv.weight"].shape[1]
+        # gather fused into aft_vq_conv (vqvae_modules.py:557-564 -> vqvae_1d_sc.py:259-261): the 1x1 conv of a
+        # concatenation of G codebook rows is a sum of G table rows, T_g = C_g . W[:, gD:(g+1)D]^T  (fp64 product,
+        # stored fp32; G x K x 1024 = 2 MB)
+        wa = sd["decoder.aft_vq_conv.weight"].double()
+        wa = wa[:, :, 0] if wa.dim() == 3 else wa                                   # [N, G*D]
+        D = self.code_dim
+        self.aft_table = torch.stack([self.codebooks[g].double() @ wa[:, g * D:(g + 1) * D].t()
+                                      for g in range(groups)]).float().contiguous()        # [G, K, N]
+        self.aft_bias = sd["decoder.aft_vq_conv.bias"].float().contiguous()
 
 
 def _stack_steps(plan, x, ws, B, device):
     """Res_CNR_Stack.forward (vqvae_modules.py:238-245): 2 x (conv+BN+LeakyReLU), conv+BN, + x, ReLU."""
-    t1 = RowBuf(B, x.T, x.C, 1, device=device)
-    t2 = RowBuf(B, x.T, x.C, 1, device=device)
-    out = RowBuf(B, x.T, x.C, 1, device=device)
+    sp = x.lo is not None
+    t1 = RowBuf(B, x.T, x.C, 1, device=device, split=sp)
+    t2 = RowBuf(B, x.T, x.C, 1, device=device, split=sp)
+    out = RowBuf(B, x.T, x.C, 1, device=device, split=sp)
     plan.conv(x, ws[0], t1, k=3, act=ACT_LEAKY)
     plan.conv(t1, ws[1], t2, k=3, act=ACT_LEAKY)
     plan.conv(t2, ws[2], out, k=3, act=ACT_RELU, residual=x)
@@ -332,10 +425,11 @@ class EncoderPlan:
         p = self.plan = Plan(dev)
         L = _lib.lib()
         self.poses = torch.zeros(B, W.in_dim, T, dtype=F32, device=dev)
-        x0 = RowBuf(B, T, _ceil(W.in_dim, 64), 1, device=dev)
-        p.call(L.pt_pack_rows, self.poses.data_ptr(), None, None, 0, x0.t.data_ptr(), B, W.in_dim, T, x0.Tp, x0.H,
-               x0.C, 0, 0)
-        h = RowBuf(B, T, 256, 1, device=dev)
+        # the encoder runs in split-bf16 arithmetic whatever the decoder's precision (see VQVAEWeights)
+        x0 = RowBuf(B, T, _ceil(W.in_dim, 64), 1, device=dev, split=True)
+        p.call(L.pt_pack_rows, self.poses.data_ptr(), None, None, 0, x0.t.data_ptr(), x0.lo.data_ptr(), B, W.in_dim, T,
+               x0.Tp, x0.H, x0.C, 0, 0)
+        h = RowBuf(B, T, 256, 1, device=dev, split=True)
         p.conv(x0, W.enc_project, h, k=3, act=ACT_LEAKY)
         self.stages = [("project", h)]
         chans = [256, 512, 1024]
@@ -343,7 +437,7 @@ class EncoderPlan:
             h = _stack_steps(p, h, W.enc_stacks[i], B, dev)
             self.stages.append(("_enc_%d" % (i + 1), h))
             if i < 3:
-                d = RowBuf(B, (h.T - 2) // 2 + 1, chans[i], 1, device=dev)
+                d = RowBuf(B, (h.T - 2) // 2 + 1, chans[i], 1, device=dev, split=True)
                 p.conv(h, W.enc_downs[i], d, k=4, stride=2, pad=1, act=ACT_LEAKY)
                 h = d
                 self.stages.append(("_down_%d" % (i + 1), h))
@@ -352,7 +446,7 @@ class EncoderPlan:
         p.conv(h, W.pre_vq, self.z, k=1)
         self.codes = torch.zeros(B, self.Tq, W.groups, dtype=torch.int64, device=dev)
         zt = self.z.t
-        p.call(L.pt_pq_search, zt.data_ptr(), self.z.Tp * 512, 1, 512, B, self.Tq, W.groups, 128, 128,
+        p.call(L.pt_pq_search, zt.data_ptr(), self.z.Tp * 512, 1, 512, B, self.Tq, W.groups, W.n_codes, W.code_dim,
                W.codebooks.data_ptr(), self.codes.data_ptr(), None, None, None)
         p.keep += [x0]
 
@@ -376,25 +470,32 @@ class DecoderPlan:
         p = self.plan = Plan(dev)
         L = _lib.lib()
         self.bad = torch.zeros(1, dtype=torch.int32, device=dev)
-        e = RowBuf(B, Tq, 512, 0, device=dev)
+        sp = W.precise
+        h = RowBuf(B, Tq, W.aft_table.shape[2], 1, device=dev, split=sp)
         if from_latents:
             # VQ.decode(latents, None) on arbitrary [B, 512, T'] fp32 latents (scripts/demo.py:152-153)
             self.codes = None
-            self.latents = torch.zeros(B, 512, Tq, dtype=F32, device=dev)
-            p.call(L.pt_pack_rows, self.latents.data_ptr(), None, None, 0, e.t.data_ptr(), B, 512, Tq, e.Tp, 0, 512, 0, 0)
+            Cl = W.groups * W.code_dim
+            e = RowBuf(B, Tq, Cl, 0, device=dev, split=sp)
+            self.latents = torch.zeros(B, Cl, Tq, dtype=F32, device=dev)
+            p.call(L.pt_pack_rows, self.latents.data_ptr(), None, None, 0, e.t.data_ptr(), _ptr(e.lo), B, Cl, Tq, e.Tp, 0,
+                   Cl, 0, 0)
+            p.conv(e, W.aft_vq, h, k=1)
+            p.keep += [e]
         else:
+            # codebook gather + dequant fused into the decoder's first conv: G table rows summed per output row
             self.codes = codes if codes is not None else torch.zeros(B, Tq, W.groups, dtype=torch.int64, device=dev)
-            p.call(L.pt_pq_gather, self.codes.data_ptr(), int(self.codes.dtype == torch.int64), W.codebooks.data_ptr(),
-                   e.t.data_ptr(), 1, e.Tp * 512, 1, 512, B, Tq, W.groups, 128, 128, self.bad.data_ptr())
-        h = RowBuf(B, Tq, 1024, 1, device=dev)
-        p.conv(e, W.aft_vq, h, k=1)
+            p.call(L.pt_pq_gather_conv1x1, self.codes.data_ptr(), int(self.codes.dtype == torch.int64),
+                   W.aft_table.data_ptr(), W.aft_bias.data_ptr(), h.t.data_ptr() + 2 * h.H * h.C,
+                   (h.lo.data_ptr() + 2 * h.H * h.C) if sp else None, h.Tp * h.C, h.C, B, Tq, W.groups, W.n_codes, h.C,
+                   self.bad.data_ptr(), flops=2.0 * B * Tq * h.C * W.groups * W.code_dim)
         self.stages = [("aft_vq_conv", h)]
         chans = [512, 256, 256]
         for i in range(4):
             h = _stack_steps(p, h, W.dec_stacks[i], B, dev)
             self.stages.append(("_dec_%d" % (i + 1), h))
             if i < 3:
-                u = RowBuf(B, 2 * h.T, chans[i], 1, device=dev)
+                u = RowBuf(B, 2 * h.T, chans[i], 1, device=dev, split=sp)
                 p.convT(h, W.dec_ups[i], u, act=ACT_LEAKY)
                 h = u
                 self.stages.append(("_up_%d" % (i + 2), h))
@@ -402,8 +503,7 @@ class DecoderPlan:
         self.out = torch.zeros(B, W.in_dim, self.T_out, dtype=F32, device=dev)
         w = W.dec_project
         p.gemm(h.t, B * h.Tp, h.C, w, self.out, M=B * h.Tp, C_=h.C, base_row=h.H, rows_per_sample=h.Tp, t_valid=h.T,
-               oss=W.in_dim * self.T_out, ors=1, ocs=self.T_out)
-        p.keep += [e]
+               oss=W.in_dim * self.T_out, ors=1, ocs=self.T_out, a_lo=h.lo)
 
     def run(self, codes=None, latents=None):
         if codes is not None:
@@ -425,13 +525,13 @@ D_MODEL, N_HEADS, HEAD_DIM = 512, 8, 64
 class StyleWeights:
     """One StylizationBlock_V3 ('sb'): LN affine, per-class [scale | shift] table, output Linear."""
 
-    def __init__(self, sd, p, class_embed, device):
+    def __init__(self, sd, p, class_embed, device, split=False):
         self.gamma = sd[p + ".norm_2.weight"].float().to(device).contiguous()
         self.beta = sd[p + ".norm_2.bias"].float().to(device).contiguous()
         w, b = sd[p + ".emb_layers_2.1.weight"].float().to(device), sd[p + ".emb_layers_2.1.bias"].float().to(device)
         # emb_layers_2 = Linear(SiLU(class_embed[label])) depends on the label only: tabulate it per class (fp32)
         self.mod = torch.nn.functional.linear(torch.nn.functional.silu(class_embed), w, b).contiguous()   # [n_classes, 1024]
-        self.out = prep_linear(sd[p + ".out_layers_2.2.weight"], sd[p + ".out_layers_2.2.bias"], device)
+        self.out = prep_linear(sd[p + ".out_layers_2.2.weight"], sd[p + ".out_layers_2.2.bias"], device, split=split)
         # fused epilogue form:  LN(h)*(1+scale)+shift = (h-mean)*rstd * A[c] + B[c]
         scale, shift = self.mod[:, :D_MODEL], self.mod[:, D_MODEL:]
         self.norm_a = (self.gamma[None] * (1 + scale)).contiguous()
@@ -439,29 +539,31 @@ class StyleWeights:
 
 
 class LayerWeights:
-    def __init__(self, sd, p, class_embed, device):
+    def __init__(self, sd, p, class_embed, device, split=False):
         C_ = D_MODEL
+        lin = lambda w, b: prep_linear(w, b, device, split=split)
         Wi, bi = sd[p + ".self_attn.in_proj_weight"], sd[p + ".self_attn.in_proj_bias"]
-        self.qkv = prep_linear(Wi, bi, device)
-        self.sa_out = prep_linear(sd[p + ".self_attn.out_proj.weight"], sd[p + ".self_attn.out_proj.bias"], device)
+        self.qkv = lin(Wi, bi)
+        self.sa_out = lin(sd[p + ".self_attn.out_proj.weight"], sd[p + ".self_attn.out_proj.bias"])
         Wc, bc = sd[p + ".multihead_attn.in_proj_weight"], sd[p + ".multihead_attn.in_proj_bias"]
-        self.ca_q = prep_linear(Wc[:C_], bc[:C_], device)
+        self.ca_q = lin(Wc[:C_], bc[:C_])
         self.ca_kv_w, self.ca_kv_b = Wc[C_:], bc[C_:]          # stacked across layers by the stack builder
-        self.ca_out = prep_linear(sd[p + ".multihead_attn.out_proj.weight"], sd[p + ".multihead_attn.out_proj.bias"], device)
-        self.ff1 = prep_linear(sd[p + ".linear1.weight"], sd[p + ".linear1.bias"], device)
-        self.ff2 = prep_linear(sd[p + ".linear2.weight"], sd[p + ".linear2.bias"], device)
+        self.ca_out = lin(sd[p + ".multihead_attn.out_proj.weight"], sd[p + ".multihead_attn.out_proj.bias"])
+        self.ff1 = lin(sd[p + ".linear1.weight"], sd[p + ".linear1.bias"])
+        self.ff2 = lin(sd[p + ".linear2.weight"], sd[p + ".linear2.bias"])
         self.norms = [(sd[p + ".norm%d.weight" % i].float().to(device).contiguous(),
                        sd[p + ".norm%d.bias" % i].float().to(device).contiguous()) for i in (1, 2, 3)]
-        self.styles = [StyleWeights(sd, p + ".style_gourp_%d" % i, class_embed, device) for i in (1, 2, 3)]
+        self.styles = [StyleWeights(sd, p + ".style_gourp_%d" % i, class_embed, device, split) for i in (1, 2, 3)]
 
 
 class StackWeights:
-    def __init__(self, sd, prefix, class_embed, device, n_layers=6):
-        self.layers = [LayerWeights(sd, "%s.layers.%d" % (prefix, l), class_embed, device) for l in range(n_layers)]
+    def __init__(self, sd, prefix, class_embed, device, n_layers=6, split=False):
+        self.split = split
+        self.layers = [LayerWeights(sd, "%s.layers.%d" % (prefix, l), class_embed, device, split) for l in range(n_layers)]
         # cross-attention K/V projections of all layers as ONE GEMM over the (constant) memory
         w = torch.cat([lw.ca_kv_w for lw in self.layers], 0)
         b = torch.cat([lw.ca_kv_b for lw in self.layers], 0)
-        self.kv_all = prep_linear(w, b, device)
+        self.kv_all = prep_linear(w, b, device, split=split)
 
 
 class StackPlanner:
@@ -475,20 +577,24 @@ class StackPlanner:
         self.p, self.W, self.B, self.N, self.Mem = plan, W, B, N, Mem
         # fuse_style: out-proj / FF2 GEMM + style LayerNorm-modulation-SiLU in one kernel (cluster row-norm epilogue)
         # fuse_norm : style GEMM + residual + LayerNorm in one kernel (107 us vs 54 + 59 us unfused at M = 90112)
-        self.fuse_style, self.fuse_norm = fuse_style, fuse_norm
+        # split-bf16 arithmetic (W.split): GEMM operands are (hi, lo) plane pairs, everything the elementwise / attention
+        # kernels read is fp32, and the row-norm epilogues (bf16 by construction) give way to the stand-alone kernels
+        sp = self.split = W.split
+        self.fuse_style, self.fuse_norm = fuse_style and not sp, fuse_norm and not sp
         M = B * N
         self.M = M
-        z = lambda *s, dt=BF16: torch.zeros(*s, dtype=dt, device=device)
-        self.xb = z(M, D_MODEL)
-        self.memb = z(B * Mem, D_MODEL)
-        self.kv = z(B * Mem, 2 * D_MODEL * len(W.layers))
-        self.qkv = z(M, 3 * D_MODEL)
-        self.q = z(M, D_MODEL)
-        self.att = z(M, D_MODEL)
-        self.proj = z(M, D_MODEL)
-        self.sil = z(M, D_MODEL)
-        self.r = z(M, D_MODEL)
-        self.ff = z(M, 4 * D_MODEL)
+        m = lambda rows, cols, **k: Mat(rows, cols, device, **k)
+        mid = F32 if sp else BF16                    # what attention / LayerNorm kernels consume
+        self.xb = m(M, D_MODEL, split=sp)
+        self.memb = m(B * Mem, D_MODEL, split=sp)
+        self.kv = m(B * Mem, 2 * D_MODEL * len(W.layers), dtype=mid)
+        self.qkv = m(M, 3 * D_MODEL, dtype=mid)
+        self.q = m(M, D_MODEL, dtype=mid)
+        self.att = m(M, D_MODEL, split=sp)
+        self.proj = m(M, D_MODEL, dtype=mid)
+        self.sil = m(M, D_MODEL, split=sp)
+        self.r = m(M, D_MODEL, dtype=mid)
+        self.ff = m(M, 4 * D_MODEL, split=sp)
         self.labels = labels
 
     def record_memory_kv(self):
@@ -506,35 +612,44 @@ class StackPlanner:
             p.linear(a_t, M, w_proj, self.sil, row_norm=1, norm_a=st.norm_a, norm_b=st.norm_b, labels=self.labels,
                      label_rows=self.N)
         else:
+            f32 = int(self.split)
             p.linear(a_t, M, w_proj, self.proj)
-            p.call(L.pt_ln_mod_silu512, self.proj.data_ptr(), 0, st.gamma.data_ptr(), st.beta.data_ptr(), st.mod.data_ptr(),
-                   self.labels.data_ptr(), self.N, self.sil.data_ptr(), M)
+            p.call(L.pt_ln_mod_silu512, self.proj.t.data_ptr(), f32, st.gamma.data_ptr(), st.beta.data_ptr(),
+                   st.mod.data_ptr(), self.labels.data_ptr(), self.N, self.sil.t.data_ptr(), _ptr(self.sil.lo), M)
         if self.fuse_norm:
             p.linear(self.sil, M, st.out, self.xb, residual=self.xb, rss=0, rrs=D_MODEL, row_norm=2, norm_a=g, norm_b=b)
             return
         p.linear(self.sil, M, st.out, self.r)
         # the residual add rides in the LayerNorm pass (a row-local read) instead of the GEMM epilogue
-        p.call(L.pt_layernorm512, self.r.data_ptr(), 0, self.xb.data_ptr(), g.data_ptr(), b.data_ptr(), None,
-               self.xb.data_ptr(), M)
+        p.call(L.pt_layernorm512, self.r.t.data_ptr(), int(self.split), self.xb.t.data_ptr(), _ptr(self.xb.lo), g.data_ptr(),
+               b.data_ptr(), None, self.xb.t.data_ptr(), _ptr(self.xb.lo), M)
 
     def record_layers(self):
         L = _lib.lib()
         p, M, B, N, Mem = self.p, self.M, self.B, self.N, self.Mem
         scale = 1.0 / math.sqrt(HEAD_DIM)
         nl = len(self.W.layers)
+        es = 4 if self.split else 2                      # bytes per q / k / v element
+
+        def attention(qp, qs, kp, ks, vp, vs, Nk):
+            if self.split:
+                p.call(L.pt_attention_f32, qp, qs, kp, ks, vp, vs, self.att.t.data_ptr(), self.att.lo.data_ptr(), D_MODEL,
+                       B, N_HEADS, HEAD_DIM, N, Nk, scale)
+            else:
+                p.call(L.pt_attention, qp, qs, kp, ks, vp, vs, self.att.t.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM, N, Nk,
+                       scale)
+
         for l, lw in enumerate(self.W.layers):
             # self attention
             p.linear(self.xb, M, lw.qkv, self.qkv)
-            p.call(L.pt_attention, self.qkv.data_ptr(), 3 * D_MODEL, self.qkv.data_ptr() + 2 * D_MODEL, 3 * D_MODEL,
-                   self.qkv.data_ptr() + 4 * D_MODEL, 3 * D_MODEL, self.att.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM,
-                   N, N, scale)
+            qkv = self.qkv.t.data_ptr()
+            attention(qkv, 3 * D_MODEL, qkv + es * D_MODEL, 3 * D_MODEL, qkv + es * 2 * D_MODEL, 3 * D_MODEL, N)
             self._sublayer_tail(lw, 0, self.att, lw.sa_out)
             # cross attention over the memory
             p.linear(self.xb, M, lw.ca_q, self.q)
             kv_stride = 2 * D_MODEL * nl
-            kptr = self.kv.data_ptr() + 2 * (l * 2 * D_MODEL)
-            p.call(L.pt_attention, self.q.data_ptr(), D_MODEL, kptr, kv_stride, kptr + 2 * D_MODEL, kv_stride,
-                   self.att.data_ptr(), D_MODEL, B, N_HEADS, HEAD_DIM, N, Mem, scale)
+            kptr = self.kv.t.data_ptr() + es * (l * 2 * D_MODEL)
+            attention(self.q.t.data_ptr(), D_MODEL, kptr, kv_stride, kptr + es * D_MODEL, kv_stride, Mem)
             self._sublayer_tail(lw, 1, self.att, lw.ca_out)
             # feed forward
             p.linear(self.xb, M, lw.ff1, self.ff, act=ACT_RELU)
@@ -552,21 +667,24 @@ CHOICE_TEMPERATURE = 4.5
 
 
 class PredictorWeights:
-    def __init__(self, state, device):
+    def __init__(self, state, device, precision="bf16"):
         dev = device
         aud = {k: v.to(dev) for k, v in state["AudEnc"].items() if torch.is_tensor(v)}
         sd = {k: v.to(dev) for k, v in state["Predictor"].items() if torch.is_tensor(v)}
         self.device = dev
+        self.precision = precision
+        sp = self.precise = _check_precision(precision)
         # AudEnc (ConditionEncoder, vqvae_1d_sc.py:70-91)
         self.aud_map = prep_conv(aud["feature_map.0.weight"], aud["feature_map.0.bias"], dev,
-                                 bn=_bn_scale_shift(aud, "feature_map.1"))
+                                 bn=_bn_scale_shift(aud, "feature_map.1"), split=sp)
         self.aud_downs = [prep_conv(aud["_down_%d.conv.weight" % i], aud["_down_%d.conv.bias" % i], dev,
                                     bn=_bn_scale_shift(aud, "_down_%d.norm" % i),
-                                    extra=(aud["_down_%d.residual_layer.weight" % i], aud["_down_%d.residual_layer.bias" % i]))
+                                    extra=(aud["_down_%d.residual_layer.weight" % i], aud["_down_%d.residual_layer.bias" % i]),
+                                    split=sp)
                           for i in (1, 2, 3)]
         # context encoder (predictornet.py:31-48, gated_pixelcnn_1d.py:39-83)
         self.mot_dim = sd["motion_embedding.weight"].shape[1] - 1
-        self.embed = prep_conv(sd["motion_embedding.weight"], sd["motion_embedding.bias"], dev)
+        self.embed = prep_conv(sd["motion_embedding.weight"], sd["motion_embedding.bias"], dev, split=sp)
         self.enc = []
         for i in range(10):
             p = "enc.%d" % i
@@ -574,10 +692,10 @@ class PredictorWeights:
             stride = 2 if (p + ".conv.weight") in sd else 1
             item = dict(k=k, stride=stride, pad=3 if k == 7 else 1,
                         cin=sd[p + ".vert_stack.weight"].shape[1], dim=sd[p + ".res.weight"].shape[0],
-                        vert=prep_conv(sd[p + ".vert_stack.weight"], sd[p + ".vert_stack.bias"], dev, gate=True),
-                        res=prep_linear(sd[p + ".res.weight"], sd[p + ".res.bias"], dev))
+                        vert=prep_conv(sd[p + ".vert_stack.weight"], sd[p + ".vert_stack.bias"], dev, gate=True, split=sp),
+                        res=prep_linear(sd[p + ".res.weight"], sd[p + ".res.bias"], dev, split=sp))
             if stride == 2:
-                item["skip"] = prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev)
+                item["skip"] = prep_conv(sd[p + ".conv.weight"], sd[p + ".conv.bias"], dev, split=sp)
             self.enc.append(item)
         # PTransformer
         d = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
@@ -587,10 +705,10 @@ class PredictorWeights:
         self.PE = d["PE.position_encoding.weight"].double()
         self.PPE = d["product_PE.position_encoding.weight"].double()
         self.groups = self.PPE.shape[0] - 1
-        self.condi = prep_linear(d["condi_emb.weight"], d["condi_emb.bias"], dev)
-        self.stack = StackWeights(d, "transformer_decoder", self.class_embed, dev)
-        self.head0 = prep_linear(d["output_conv.0.weight"], d["output_conv.0.bias"], dev)
-        self.head1 = prep_linear(d["output_conv.2.weight"], d["output_conv.2.bias"], dev)
+        self.condi = prep_linear(d["condi_emb.weight"], d["condi_emb.bias"], dev, split=sp)
+        self.stack = StackWeights(d, "transformer_decoder", self.class_embed, dev, split=sp)
+        self.head0 = prep_linear(d["output_conv.0.weight"], d["output_conv.0.bias"], dev, split=sp)
+        self.head1 = prep_linear(d["output_conv.2.weight"], d["output_conv.2.bias"], dev, split=sp)
         self.n_codes = d["output_conv.2.weight"].shape[0]
 
 
@@ -616,37 +734,41 @@ class PredictorPlan:
         self.labels = torch.zeros(B, dtype=torch.int32, device=dev)
         # ---------------- plan A: condition (AudEnc + context encoder + memory K/V) ----------------
         pa = self.plan_cond = Plan(dev)
-        xa = RowBuf(B, T, 768, 0, device=dev)
-        pa.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xa.t.data_ptr(), B, 768, T, xa.Tp, xa.H, xa.C, 0, 0)
-        h = RowBuf(B, T, 256, 1, device=dev)
+        sp = PW.precise
+        RB = lambda *a, **k: RowBuf(*a, device=dev, split=sp, **k)
+        xa = RB(B, T, 768, 0)
+        pa.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xa.t.data_ptr(), _ptr(xa.lo), B, 768, T, xa.Tp, xa.H,
+                xa.C, 0, 0)
+        h = RB(B, T, 256, 1)
         pa.conv(xa, PW.aud_map, h, k=1, act=ACT_LEAKY, slope=0.1)
         Tq = T
         for i in range(3):
             Tq = (Tq - 2) // 2 + 1
         self.Tq = Tq
         self.N = Tq * G
-        cond = RowBuf(B, Tq, 768, 0, device=dev)                   # [mm (512) | audio (256)]  (predictornet.py:93-95)
+        cond = RB(B, Tq, 768, 0)                                   # [mm (512) | audio (256)]  (predictornet.py:93-95)
         for i in range(3):
             To = (h.T - 2) // 2 + 1
             if i < 2:
-                d = RowBuf(B, To, 256, 1, device=dev)
+                d = RB(B, To, 256, 1)
                 pa.conv(h, PW.aud_downs[i], d, k=4, stride=2, pad=1, act=ACT_LEAKY)
                 h = d
             else:
                 pa.conv(h, PW.aud_downs[i], cond, k=4, stride=2, pad=1, act=ACT_LEAKY, out_c_off=512)
-        xm = RowBuf(B, T, _ceil(PW.mot_dim + 1, 64), 0, device=dev)
-        pa.call(L.pt_pack_rows, self.gt.data_ptr(), self.mask.data_ptr(), None, 0, xm.t.data_ptr(), B, PW.mot_dim, T,
-                xm.Tp, xm.H, xm.C, 0, 1)
+        xm = RB(B, T, _ceil(PW.mot_dim + 1, 64), 0)
+        pa.call(L.pt_pack_rows, self.gt.data_ptr(), self.mask.data_ptr(), None, 0, xm.t.data_ptr(), _ptr(xm.lo), B,
+                PW.mot_dim, T, xm.Tp, xm.H, xm.C, 0, 1)
+        # (a 0 / 1 mask is exact in bf16: the lo plane of the mask channel stays zero)
         pa.call(L.pt_pack_mask, self.mask.data_ptr(), xm.t.data_ptr(), B, T, xm.Tp, xm.H, xm.C, PW.mot_dim, 0)
-        mm = RowBuf(B, T, 128, 3, device=dev)
+        mm = RB(B, T, 128, 3)
         pa.conv(xm, PW.embed, mm, k=1)
         self.ctx_stages = [("motion_embedding", mm)]
         for i, e in enumerate(PW.enc):
             To = mm.T if e["stride"] == 1 else (mm.T - 2) // 2 + 1
-            gate = RowBuf(B, To, e["dim"], 0, device=dev)
+            gate = RB(B, To, e["dim"], 0)
             pa.conv(mm, e["vert"], gate, k=e["k"], stride=e["stride"], pad=e["pad"], act=ACT_GATE)
             if e["stride"] == 2:
-                skip = RowBuf(B, To, e["dim"], 0, device=dev)
+                skip = RB(B, To, e["dim"], 0)
                 pa.conv(mm, e["skip"], skip, k=4, stride=2, pad=1)
             else:
                 skip = mm
@@ -655,7 +777,7 @@ class PredictorPlan:
                 pa.conv(gate, e["res"], cond, k=1, residual=skip, out_c_off=0)
                 nxt = cond
             else:
-                nxt = RowBuf(B, To, e["dim"], 1, device=dev)
+                nxt = RB(B, To, e["dim"], 1)
                 pa.conv(gate, e["res"], nxt, k=1, residual=skip)
             mm = nxt
             self.ctx_stages.append(("enc.%d" % i, mm))
@@ -668,9 +790,9 @@ class PredictorPlan:
         self.c_pe32 = c_pe.float().contiguous().to(dev)
         self.stack = StackPlanner(pa, PW.stack, B, self.N, Tq, self.labels, dev)
         # condition embedding 1x1 (768 -> 512) + PE, rounded once to bf16 (only ever a GEMM operand)
-        pa.gemm(cond.t, B * cond.Tp, 768, PW.condi, self.stack.memb, M=B * cond.Tp, C_=768, base_row=0,
+        pa.gemm(cond.t, B * cond.Tp, 768, PW.condi, self.stack.memb.t, M=B * cond.Tp, C_=768, base_row=0,
                 rows_per_sample=cond.Tp, t_valid=Tq, oss=Tq * D_MODEL, ors=D_MODEL, residual=self.c_pe32, rss=0,
-                rrs=D_MODEL)
+                rrs=D_MODEL, a_lo=cond.lo, out_lo=self.stack.memb.lo)
         self.stack.record_memory_kv()
         # ---------------- plan B: one MaskGIT iteration (embed -> 6 layers -> logits) ----------------
         pb = self.plan_iter = Plan(dev)
@@ -679,9 +801,9 @@ class PredictorPlan:
         self.cur = torch.full((B, self.N), MASK_ID, dtype=torch.int32, device=dev)
         self.bad = torch.zeros(1, dtype=torch.int32, device=dev)
         pb.call(L.pt_embed_tokens512, self.cur.data_ptr(), PW.tok_emb.data_ptr(), PW.n_emb, self.x_pe64.data_ptr(), self.N,
-                None, self.stack.xb.data_ptr(), M, self.bad.data_ptr())
+                None, self.stack.xb.t.data_ptr(), _ptr(self.stack.xb.lo), M, self.bad.data_ptr())
         self.stack.record_layers()
-        self.h1 = torch.zeros(M, D_MODEL, dtype=BF16, device=dev)
+        self.h1 = Mat(M, D_MODEL, dev, split=sp)
         self.logits = torch.zeros(M, PW.n_codes, dtype=F32, device=dev)
         pb.linear(self.stack.xb, M, PW.head0, self.h1, act=ACT_RELU)
         pb.linear(self.h1, M, PW.head1, self.logits)
@@ -730,10 +852,15 @@ class PredictorPlan:
         self.dec.plan.run()
         return self.out
 
-    def run(self, aud, gt, mask, labels, noise=None, generator=None):
+    def run(self, aud, gt, mask, labels, noise=None, generator=None, force_codes=None):
         """Full infer_to_code for a batch.  noise = (u, gumbel) [T, B, N] to inject, else drawn on the device.
+        force_codes [B, T', G]: teacher forcing -- skip the sampler and decode these codes (parity tests).
         Returns (poses [B,376,T] fp32, codes [B,T',G] int32) -- views of plan-owned buffers."""
         self.aud.copy_(aud); self.gt.copy_(gt); self.mask.copy_(mask); self.labels.copy_(labels)
+        if force_codes is not None:
+            self.cur.copy_(force_codes.reshape(self.B, -1))
+            self.dec.plan.run()
+            return self.out, self.codes
         if noise is not None:
             self.u.copy_(noise[0]); self.gumbel.copy_(noise[1])
         else:
@@ -770,19 +897,21 @@ class PredictorPlan:
 # ----------------------------------------------------------------------------------------------
 
 class RefinerWeights:
-    def __init__(self, state, device):
+    def __init__(self, state, device, precision="bf16"):
         dev = device
         sd = {k: v.to(dev) for k, v in state["HFTransformer"].items() if torch.is_tensor(v)}
         self.device = dev
+        self.precision = precision
+        sp = self.precise = _check_precision(precision)
         self.in_dim = sd["input_conv.weight"].shape[1]
         self.aud_dim = sd["audio_conv.weight"].shape[1] - 2
         self.class_embed = sd["class_embed.weight"].float()
         self.PE = sd["PE.position_encoding.weight"].double()
-        self.input_conv = prep_linear(sd["input_conv.weight"], sd["input_conv.bias"], dev)
-        self.audio_conv = prep_linear(sd["audio_conv.weight"], sd["audio_conv.bias"], dev)
-        self.stack = StackWeights(sd, "transformer_decoder", self.class_embed, dev)
-        self.head0 = prep_linear(sd["output_conv.0.weight"], sd["output_conv.0.bias"], dev)
-        self.head1 = prep_linear(sd["output_conv.2.weight"], sd["output_conv.2.bias"], dev)
+        self.input_conv = prep_linear(sd["input_conv.weight"], sd["input_conv.bias"], dev, split=sp)
+        self.audio_conv = prep_linear(sd["audio_conv.weight"], sd["audio_conv.bias"], dev, split=sp)
+        self.stack = StackWeights(sd, "transformer_decoder", self.class_embed, dev, split=sp)
+        self.head0 = prep_linear(sd["output_conv.0.weight"], sd["output_conv.0.bias"], dev, split=sp)
+        self.head1 = prep_linear(sd["output_conv.2.weight"], sd["output_conv.2.bias"], dev, split=sp)
 
 
 class RefinerPlan:
@@ -800,26 +929,29 @@ class RefinerPlan:
         p = self.plan = Plan(dev)
         M = B * T
         # blank = gt*mask + interp(pred)*(1-mask)  -> rows [B*T, 384]
-        xin = RowBuf(B, T, _ceil(RW.in_dim, 64), 0, device=dev, even=False)      # any T (odd tail windows too)
+        sp = RW.precise
+        xin = RowBuf(B, T, _ceil(RW.in_dim, 64), 0, device=dev, even=False, split=sp)      # any T (odd tail windows too)
         p.call(L.pt_pack_rows, self.gt.data_ptr(), self.mask.data_ptr(), self.pred.data_ptr(), self.T_pred, xin.t.data_ptr(),
-               B, RW.in_dim, T, xin.Tp, 0, xin.C, 0, 2)
+               _ptr(xin.lo), B, RW.in_dim, T, xin.Tp, 0, xin.C, 0, 2)
         # condition = cat(audio, one_hot(mask))  -> rows [B*T, 832]
-        xc = RowBuf(B, T, _ceil(RW.aud_dim + 2, 64), 0, device=dev, even=False)
-        p.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xc.t.data_ptr(), B, RW.aud_dim, T, xc.Tp, 0, xc.C, 0, 0)
+        xc = RowBuf(B, T, _ceil(RW.aud_dim + 2, 64), 0, device=dev, even=False, split=sp)
+        p.call(L.pt_pack_rows, self.aud.data_ptr(), None, None, 0, xc.t.data_ptr(), _ptr(xc.lo), B, RW.aud_dim, T, xc.Tp, 0,
+               xc.C, 0, 0)
         p.call(L.pt_pack_mask, self.mask.data_ptr(), xc.t.data_ptr(), B, T, xc.Tp, 0, xc.C, RW.aud_dim, 1)
         self.pe32 = RW.PE[1:T + 1].float().contiguous().to(dev)
         self.stack = StackPlanner(p, RW.stack, B, T, T, self.labels, dev)
         st = self.stack
         # x = float32(input_conv(blank) + PE)   (RTransformer.py:211-214)
-        p.linear(xin.t, M, RW.input_conv, st.xb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
-        p.linear(xc.t, M, RW.audio_conv, st.memb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
+        p.linear(xin, M, RW.input_conv, st.xb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
+        p.linear(xc, M, RW.audio_conv, st.memb, residual=self.pe32, rss=0, rrs=D_MODEL, rows_per_sample=T)
         st.record_memory_kv()
         st.record_layers()
-        self.h1 = torch.zeros(M, 1024, dtype=BF16, device=dev)
+        self.h1 = Mat(M, 1024, dev, split=sp)
         self.raw = f32(B, RW.in_dim, T)
         p.linear(st.xb, M, RW.head0, self.h1, act=ACT_RELU)
         w = RW.head1
-        p.gemm(self.h1, M, 1024, w, self.raw, M=M, C_=1024, rows_per_sample=T, t_valid=T, oss=RW.in_dim * T, ors=1, ocs=T)
+        p.gemm(self.h1.t, M, 1024, w, self.raw, M=M, C_=1024, rows_per_sample=T, t_valid=T, oss=RW.in_dim * T, ors=1, ocs=T,
+               a_lo=self.h1.lo)
         self.out = f32(B, RW.in_dim, T)
         p.call(L.pt_interp_blend, self.gt.data_ptr(), self.mask.data_ptr(), self.raw.data_ptr(), T, self.out.data_ptr(), B,
                RW.in_dim, T, 1)
@@ -855,23 +987,25 @@ class EmbeddingWeights:
     LeakyReLU 0.2) and the MLP 1280 -> 512 -> 256 -> 128 -> fc_mu 128.  `nn.LeakyReLU(True)` in the MLP is
     negative_slope = 1.0, i.e. the identity (embedding_net.py:71-77), reproduced as such."""
 
-    def __init__(self, sd, device, prefix="pose_encoder."):
+    def __init__(self, sd, device, prefix="pose_encoder.", precision="bf16"):
         g = lambda k: sd[prefix + k]
         self.dim = g("net.0.0.weight").shape[1]
-        self.c1 = prep_conv(g("net.0.0.weight"), g("net.0.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.0.1"))
-        self.c2 = prep_conv(g("net.1.0.weight"), g("net.1.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.1.1"), cin_pad=64)
-        self.c3 = prep_conv(g("net.2.0.weight"), g("net.2.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.2.1"))
-        self.c4 = prep_conv(g("net.3.weight"), g("net.3.bias"), device)
+        self.precision = precision
+        sp = self.precise = _check_precision(precision)
+        self.c1 = prep_conv(g("net.0.0.weight"), g("net.0.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.0.1"), split=sp)
+        self.c2 = prep_conv(g("net.1.0.weight"), g("net.1.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.1.1"), cin_pad=64, split=sp)
+        self.c3 = prep_conv(g("net.2.0.weight"), g("net.2.0.bias"), device, bn=_bn_scale_shift(sd, prefix + "net.2.1"), split=sp)
+        self.c4 = prep_conv(g("net.3.weight"), g("net.3.bias"), device, split=sp)
         # flatten(1) of [B, 32, 40] is channel-major; our rows are [B, 40, 64]: W'[n, t*64 + c] = W[n, c*40 + t]
         w = g("out_net.0.weight").float()                                   # [512, 1280]
         s0, h0 = _bn_scale_shift(sd, prefix + "out_net.1")
         wp = torch.zeros(512, 40, 64)
         wp[:, :, :32] = w.view(512, 32, 40).permute(0, 2, 1)
-        self.l1 = prep_linear(wp.reshape(512, 2560) * s0[:, None], g("out_net.0.bias").float() * s0 + h0, device)
+        self.l1 = prep_linear(wp.reshape(512, 2560) * s0[:, None], g("out_net.0.bias").float() * s0 + h0, device, split=sp)
         s1, h1 = _bn_scale_shift(sd, prefix + "out_net.4")
-        self.l2 = prep_linear(g("out_net.3.weight").float() * s1[:, None], g("out_net.3.bias").float() * s1 + h1, device)
-        self.l3 = prep_linear(g("out_net.6.weight"), g("out_net.6.bias"), device)
-        self.mu = prep_linear(g("fc_mu.weight"), g("fc_mu.bias"), device)
+        self.l2 = prep_linear(g("out_net.3.weight").float() * s1[:, None], g("out_net.3.bias").float() * s1 + h1, device, split=sp)
+        self.l3 = prep_linear(g("out_net.6.weight"), g("out_net.6.bias"), device, split=sp)
+        self.mu = prep_linear(g("fc_mu.weight"), g("fc_mu.bias"), device, split=sp)
 
 
 class EmbeddingPlan:
@@ -883,25 +1017,27 @@ class EmbeddingPlan:
         L = _lib.lib()
         T = 90
         self.poses = torch.zeros(B, W.dim, T, dtype=F32, device=dev)
-        x0 = RowBuf(B, T, _ceil(W.dim, 64), 0, device=dev)
-        p.call(L.pt_pack_rows, self.poses.data_ptr(), None, None, 0, x0.t.data_ptr(), B, W.dim, T, x0.Tp, 0, x0.C, 0, 0)
-        h1, h2 = RowBuf(B, 88, 64, 0, device=dev), RowBuf(B, 86, 64, 0, device=dev)
-        h3, h4 = RowBuf(B, 42, 64, 0, device=dev), RowBuf(B, 40, 64, 0, device=dev)
+        sp = W.precise
+        RB = lambda *a: RowBuf(*a, device=dev, split=sp)
+        x0 = RB(B, T, _ceil(W.dim, 64), 0)
+        p.call(L.pt_pack_rows, self.poses.data_ptr(), None, None, 0, x0.t.data_ptr(), _ptr(x0.lo), B, W.dim, T, x0.Tp, 0,
+               x0.C, 0, 0)
+        h1, h2 = RB(B, 88, 64, 0), RB(B, 86, 64, 0)
+        h3, h4 = RB(B, 42, 64, 0), RB(B, 40, 64, 0)
 
         def valid_conv(x, w, out, act):                  # k3, stride 1, no padding: out[t] = sum_j x[t + j]
             p.gemm(x.t, x.B * x.Tp, x.C, w, out.t, M=x.B * x.Tp, C_=x.C, s=1, base_row=0, rows_per_sample=x.Tp,
-                   t_valid=out.T, oss=out.Tp * out.C, ors=out.C, act=act, slope=0.2)
+                   t_valid=out.T, oss=out.Tp * out.C, ors=out.C, act=act, slope=0.2, a_lo=x.lo, out_lo=out.lo)
 
         valid_conv(x0, W.c1, h1, ACT_LEAKY)
         valid_conv(h1, W.c2, h2, ACT_LEAKY)
         # k4, stride 2, no padding: rows viewed as [Tp / 2, 2 C]; tap j = row t + j / 2, column half j % 2
         p.gemm(h2.t, B * h2.Tp, h2.C, W.c3, h3.t, M=B * h2.Tp // 2, C_=h2.C, s=2, base_row=0, rows_per_sample=h2.Tp // 2,
-               t_valid=h3.T, oss=h3.Tp * h3.C, ors=h3.C, act=ACT_LEAKY, slope=0.2)
+               t_valid=h3.T, oss=h3.Tp * h3.C, ors=h3.C, act=ACT_LEAKY, slope=0.2, a_lo=h2.lo, out_lo=h3.lo)
         valid_conv(h3, W.c4, h4, ACT_NONE)
-        z = lambda n, dt=BF16: torch.zeros(B, n, dtype=dt, device=dev)
-        f1, f2, f3 = z(512), z(256), z(128)
-        self.out = z(128, F32)
-        p.linear(h4.t, B, W.l1, f1)                      # A = the [B, 40 * 64] view of the conv output
+        f1, f2, f3 = Mat(B, 512, dev, split=sp), Mat(B, 256, dev, split=sp), Mat(B, 128, dev, split=sp)
+        self.out = torch.zeros(B, 128, dtype=F32, device=dev)
+        p.linear(h4, B, W.l1, f1)                        # A = the [B, 40 * 64] view of the conv output
         p.linear(f1, B, W.l2, f2)
         p.linear(f2, B, W.l3, f3)
         p.linear(f3, B, W.mu, self.out)

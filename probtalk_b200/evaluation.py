@@ -33,6 +33,40 @@ def feature_stats(feats: torch.Tensor):
     return mean, cov
 
 
+def lvd(gt_kps: torch.Tensor, pr_kps: torch.Tensor):
+    """Landmark velocity difference, LVD(gt [T, J, D], pr [B, T, J, D]) of evaluation/metrics.py:79-94 (Batch_LVD branch,
+    symmetrical = False, weight = False; the longer of the two is cut to the shorter).  Returns (mean float, per-sample
+    fp64 CUDA tensor [B])."""
+    if not (gt_kps.is_cuda and pr_kps.is_cuda):
+        raise _lib.PtError("probtalk_b200.evaluation needs CUDA tensors (no CPU fallback)")
+    if pr_kps.dim() == 3:
+        pr_kps = pr_kps.unsqueeze(0)
+    T = min(gt_kps.shape[0], pr_kps.shape[1])
+    gt = gt_kps[:T].float().contiguous()
+    pr = pr_kps[:, :T].float().contiguous()
+    B, _, J, D = pr.shape
+    assert gt.shape == (T, J, D)
+    per = torch.empty(B, dtype=torch.float64, device=gt.device)
+    mean = torch.empty(1, dtype=torch.float64, device=gt.device)
+    _lib.check(_lib.lib().pt_lvd(gt.data_ptr(), pr.data_ptr(), B, T, J, D, per.data_ptr(), mean.data_ptr(),
+                                 torch.cuda.current_stream().cuda_stream), "pt_lvd")
+    return float(mean), per
+
+
+def diversity(kps: torch.Tensor):
+    """Mean pairwise L1 distance between the B samples kps [B, seq, dim] (evaluation/metrics.py:96-110).
+    Returns (mean float, per-pair fp64 CUDA tensor [B (B - 1) / 2], pairs i < j with i outer)."""
+    if not kps.is_cuda:
+        raise _lib.PtError("probtalk_b200.evaluation needs CUDA tensors (no CPU fallback)")
+    B = kps.shape[0]
+    x = kps.float().reshape(B, -1).contiguous()
+    per = torch.empty(B * (B - 1) // 2, dtype=torch.float64, device=x.device)
+    mean = torch.empty(1, dtype=torch.float64, device=x.device)
+    _lib.check(_lib.lib().pt_diversity(x.data_ptr(), B, x.shape[1], per.data_ptr(), mean.data_ptr(),
+                                       torch.cuda.current_stream().cuda_stream), "pt_diversity")
+    return float(mean), per
+
+
 def frechet_distance(mu1, sigma1, mu2, sigma2, eps=1e-6):
     """d^2 = |mu1 - mu2|^2 + Tr(S1 + S2 - 2 sqrt(S1 S2)), same steps and fallbacks as evaluation/FGD.py:190-257."""
     from scipy import linalg

@@ -112,8 +112,9 @@ class PQLayer(M.ProductQuantizationParams):
 class VQVAE(M.VQVAE_SC):
     """VQVAE_SC with the reference's call surface (vqvae_1d_sc.py:277-324) on top of the CUDA plans."""
 
-    def __init__(self, *a, device="cuda", **k):
+    def __init__(self, *a, device="cuda", precision="bf16", **k):
         super().__init__(*a, **k)
+        self._precision = precision
         import weakref
         pq = PQLayer(self.embedding_dim, self.num_embeddings, self.groups)
         pq.__dict__["_owner"] = weakref.ref(self)
@@ -132,7 +133,7 @@ class VQVAE(M.VQVAE_SC):
 
     def weights(self):
         if self._weights is None:
-            self._weights = E.VQVAEWeights(self.state_dict(), self._device, self.groups)
+            self._weights = E.VQVAEWeights(self.state_dict(), self._device, self.groups, self._precision)
         return self._weights
 
     def _plan(self, kind, *key):
@@ -185,6 +186,10 @@ class _WrapperBase:
     def __init__(self, args, config):
         self.args, self.config = args, config
         self.device = _device(args)
+        # arithmetic of the dense ops: "bf16" (throughput) or "bf16x3" (split-bf16, fp32-grade).
+        # Not part of the reference's interface: an optional args attribute, else the PROBTALK_B200_PRECISION variable.
+        self.precision = getattr(args, "precision", None) or os.environ.get("PROBTALK_B200_PRECISION", "bf16")
+        E._check_precision(self.precision)
         self.full_dim, self.each_dim = _pose_dims(config)
         self.num_classes = _n_classes(config)
         self.global_step = 0
@@ -193,7 +198,7 @@ class _WrapperBase:
 
     def _make_vq(self, in_dim):
         m = self.config.Model
-        vq = VQVAE(in_dim, m.groups * 128, m.code_num, 1024, 2, m.groups, device=self.device)
+        vq = VQVAE(in_dim, m.groups * 128, m.code_num, 1024, 2, m.groups, device=self.device, precision=self.precision)
         vq.enable_facade()
         path = getattr(m, "vq_path", None)
         if path and os.path.exists(path):
@@ -219,7 +224,7 @@ class s2g_body_vqt(_WrapperBase):
         self.type = config.Model.vq_type
         assert self.type == "fbhe", "only the holistic 'fbhe' PQ-VAE of config/vq.json is built"
         self.VQ = VQVAE(self.full_dim, config.Model.groups * 128, config.Model.code_num, 1024, 2, config.Model.groups,
-                        device=self.device)
+                        device=self.device, precision=self.precision)
         self.VQ.enable_facade()
         self.generator = self.VQ
 
@@ -274,7 +279,7 @@ class s2g_body_predictor(_WrapperBase):
     def _plan(self, B, T):
         if self._weights is None:
             self._weights = E.PredictorWeights({"AudEnc": self.AudEnc.state_dict(), "Predictor": self.Predictor.state_dict()},
-                                               self.device)
+                                               self.device, self.precision)
         return self._plans.get((B, T), lambda: E.PredictorPlan(self._weights, self.VQ.weights(), B, T, self.Predictor.T))
 
     def _infer(self, aud, id, B, gt_poses, mask, noise=None):
@@ -324,7 +329,7 @@ class s2g_body_refiner(_WrapperBase):
 
     def _plan(self, B, T, Tp):
         if self._weights is None:
-            self._weights = E.RefinerWeights({"HFTransformer": self.RTransformer.state_dict()}, self.device)
+            self._weights = E.RefinerWeights({"HFTransformer": self.RTransformer.state_dict()}, self.device, self.precision)
         return self._plans.get((B, T, Tp), lambda: E.RefinerPlan(self._weights, B, T, Tp))
 
     def infer_on_batch(self, aud, B=1, id=0, gt_poses=None, mask=None, pred_poses=None, **kw):

@@ -87,14 +87,23 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
          oss: int = 0, ors: int = None, ocs: int = 1, out_offset: int = 0, bias: torch.Tensor = None,
          residual: torch.Tensor = None, rss: int = 0, rrs: int = 0, res_offset: int = 0, act: int = ACT_NONE,
          slope: float = 0.2, a_rows: int = None, a_pitch: int = None, a_offset: int = 0, row_norm: int = 0,
-         norm_a: torch.Tensor = None, norm_b: torch.Tensor = None, labels: torch.Tensor = None, label_rows: int = 1):
+         norm_a: torch.Tensor = None, norm_b: torch.Tensor = None, labels: torch.Tensor = None, label_rows: int = 1,
+         a_lo: torch.Tensor = None, out_lo: torch.Tensor = None, residual_lo: torch.Tensor = None):
     """Launch the tensor-core contraction engine (see pt_gemm_bf16 in include/probtalk_b200.h).
-    ``a`` / ``out`` / ``residual`` are flat device buffers; offsets are in elements."""
-    _need_cuda(a, w, out, bias, residual)
+    ``a`` / ``out`` / ``residual`` are flat device buffers; offsets are in elements.
+    Split-bf16 arithmetic: pass ``a_lo`` (and ``out_lo`` / ``residual_lo`` for bf16 outputs / residuals) and a weight
+    of shape [N, 2 * taps * C] = [hi | lo] (``split_weight``)."""
+    _need_cuda(a, w, out, bias, residual, a_lo, out_lo, residual_lo)
     assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and w.dim() == 2
     N = w.shape[0]
-    assert w.shape[1] == taps * C_ and w.is_contiguous()
+    split = a_lo is not None
+    assert w.shape[1] == (2 if split else 1) * taps * C_ and w.is_contiguous()
     d = GemmDesc()
+    if split:
+        d.split = 1
+        d.a_lo = a_lo.data_ptr() + 2 * a_offset
+        d.out_lo = out_lo.data_ptr() + 2 * out_offset if out_lo is not None else None
+        d.residual_lo = residual_lo.data_ptr() + 2 * res_offset if residual_lo is not None else None
     d.a = a.data_ptr() + 2 * a_offset
     d.a_pitch = a_pitch if a_pitch is not None else C_
     d.a_rows = a_rows if a_rows is not None else (a.numel() - a_offset) // d.a_pitch
@@ -124,3 +133,47 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
     d.norm_classes = (norm_a.numel() // 512) if norm_a is not None else 0
     check(_lib.lib().pt_gemm_bf16(C.byref(d), _stream()), "pt_gemm_bf16")
     return out
+
+
+def split_bf16(x: torch.Tensor):
+    """fp32 tensor -> (hi, lo) bf16 pair with hi = bf16(x), lo = bf16(x - hi): the operand format of the split-bf16
+    ("bf16x3") arithmetic mode (hi + lo carries 16 mantissa bits of x)."""
+    hi = x.to(torch.bfloat16)
+    return hi, (x.float() - hi.float()).to(torch.bfloat16)
+
+
+def split_weight(w: torch.Tensor):
+    """fp32 weight matrix [N, K] -> bf16 [N, 2K] = [hi | lo], the layout pt_gemm_desc.split expects."""
+    hi, lo = split_bf16(w)
+    return torch.cat([hi, lo], dim=1).contiguous()
+
+
+def pq_gather_conv1x1(idx: torch.Tensor, table: torch.Tensor, bias: torch.Tensor, split: bool = False):
+    """Fused codebook gather + decoder entry conv (pt_pq_gather_conv1x1): idx [B, W, G], table fp32 [G, K, N], bias [N]
+    -> bf16 [B, W, N] (plus the lo plane when ``split``) and the out-of-range index counter."""
+    _need_cuda(idx, table, bias)
+    B, W, G = idx.shape
+    G2, K, N = table.shape
+    assert G2 == G and idx.dtype in (torch.int64, torch.int32) and table.dtype == torch.float32
+    idx, table, bias = idx.contiguous(), table.contiguous(), bias.contiguous()
+    out = torch.empty(B, W, N, dtype=torch.bfloat16, device=idx.device)
+    lo = torch.empty_like(out) if split else None
+    bad = torch.zeros((1,), dtype=torch.int32, device=idx.device)
+    check(_lib.lib().pt_pq_gather_conv1x1(idx.data_ptr(), int(idx.dtype == torch.int64), table.data_ptr(), bias.data_ptr(),
+                                          out.data_ptr(), _ptr(lo), W * N, N, B, W, G, K, N, bad.data_ptr(), _stream()),
+          "pt_pq_gather_conv1x1")
+    return out, lo, bad
+
+
+def attention_f32(q, k, v, B, Nq, Nk, heads=8, head_dim=64, scale=None, split=True):
+    """fp32 attention core (pt_attention_f32): q [B*Nq, heads*head_dim], k / v [B*Nk, ...] fp32 (any row stride)
+    -> (hi, lo) bf16 [B*Nq, heads*head_dim]."""
+    _need_cuda(q, k, v)
+    assert q.dtype == k.dtype == v.dtype == torch.float32
+    out = torch.empty(B * Nq, heads * head_dim, dtype=torch.bfloat16, device=q.device)
+    lo = torch.empty_like(out) if split else None
+    scale = scale if scale is not None else head_dim ** -0.5
+    check(_lib.lib().pt_attention_f32(q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+                                      out.data_ptr(), _ptr(lo), heads * head_dim, B, heads, head_dim, Nq, Nk, scale,
+                                      _stream()), "pt_attention_f32")
+    return out, lo

@@ -80,3 +80,19 @@ def test_embedding_plan_and_evaluator_vs_golden(gold):
     rm, rs = EV.feature_stats(stack(gold["feat_real"]))
     exact = EV.frechet_distance(gm.cpu().numpy(), gs.cpu().numpy(), rm.cpu().numpy(), rs.cpu().numpy())
     assert abs(exact - gold["fgd"]) < 1e-6 * max(1.0, gold["fgd"])
+
+
+@pytest.mark.gpu
+def test_evaluator_single_chunk_push_does_not_alias(gold):
+    """A push with ONE 90-frame chunk (any 90..179-frame clip): the real features must survive the generated-feature
+    extraction that follows (the extractor reuses its output buffer)."""
+    from probtalk_b200 import engine as E, evaluation as EV
+    plan = E.EmbeddingPlan(E.EmbeddingWeights(gold["state_dict"], "cuda"), 4)
+    ev = EV.EmbeddingSpaceEvaluator(plan.extract)
+    for i in range(3):
+        ev.push_samples(gold["gene"][i:i + 1].cuda(), gold["real"][i:i + 1].cuda())
+    for i in range(3):
+        fr = plan.extract(gold["real"][i:i + 1].cuda()).clone()
+        fg = plan.extract(gold["gene"][i:i + 1].cuda()).clone()
+        assert torch.equal(ev.real_feat[i], fr.t()) and torch.equal(ev.gene_feat[i], fg.t())
+        assert not torch.equal(ev.real_feat[i], ev.gene_feat[i])

@@ -70,3 +70,31 @@ def test_cfg4_predictor_refiner(gold, states):
     assert torch.allclose(poses, c["poses"], atol=5e-5, rtol=1e-4)
     out = O.refiner_infer_on_batch(aud, gt, mask, torch.tensor([c["id"]]), poses, rst["HFTransformer"])
     assert torch.allclose(out, c["refined"], atol=1e-4, rtol=1e-4)
+
+
+def test_window_oracle_replays_reference_window_vectors():
+    """oracle/window_oracle.py against tests/golden/window_vectors.pt (the reference's own loops, made by
+    oracle/make_golden_windows.py): runs anywhere, no reference tree needed."""
+    import os
+    from oracle import make_golden_windows as GW
+    from oracle import window_oracle as WO
+    from probtalk_b200 import synthetic as S
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "window_vectors.pt"), map_location="cpu",
+                      weights_only=False)
+    s = gold["seeds"]
+    vq, pst, rst = S.make_vq_state(s["vq"]), S.make_predictor_state(s["pred"]), S.make_refiner_state(s["ref"])
+    c = gold["eval"]
+    aud1, gt1, mask, noise = GW.eval_inputs()
+    B = c["B"]
+    ids = torch.tensor([c["id"]]).repeat(B)
+    out, codes = WO.windows_eval(aud1.repeat(B, 1, 1), gt1.repeat(B, 1, 1), mask, ids, pst, vq, rst["HFTransformer"], noise=noise)
+    assert all(torch.equal(a.long(), b.long()) for a, b in zip(codes, c["codes"]))
+    assert torch.allclose(out, c["poses"], atol=2e-4, rtol=1e-4)
+    d = gold["demo"]
+    ids = torch.tensor([d["id"]]).repeat(d["B"])
+    aud1, noise = GW.demo_inputs()
+    # teacher-forced with the reference's per-window codes (cheap: no sampler iterations)
+    poses, all_codes, _ = WO.windows_demo(aud1.repeat(d["B"], 1, 1), ids, pst, vq, rst["HFTransformer"],
+                                          codes=[x.long() for x in d["window_codes"]])
+    assert torch.equal(all_codes.long(), d["codes"].long())
+    assert torch.allclose(poses, d["poses"], atol=2e-4, rtol=1e-4)

@@ -163,14 +163,14 @@ def test_layernorm_kernels_and_embed():
     x = torch.randn(M, 512, device="cuda", generator=g) * 3 + 1
     gamma, beta = torch.rand(512, device="cuda", generator=g) + 0.5, torch.randn(512, device="cuda", generator=g)
     o32, o16 = torch.zeros(M, 512, device="cuda"), torch.zeros(M, 512, device="cuda", dtype=torch.bfloat16)
-    _lib.check(L.pt_layernorm512(x.data_ptr(), 1, None, gamma.data_ptr(), beta.data_ptr(), o32.data_ptr(), o16.data_ptr(), M, _st()))
+    _lib.check(L.pt_layernorm512(x.data_ptr(), 1, None, None, gamma.data_ptr(), beta.data_ptr(), o32.data_ptr(), o16.data_ptr(), None, M, _st()))
     xb16 = x.bfloat16()
     o16b = torch.zeros_like(o16)
-    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, None, gamma.data_ptr(), beta.data_ptr(), None, o16b.data_ptr(), M, _st()))
+    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, None, None, gamma.data_ptr(), beta.data_ptr(), None, o16b.data_ptr(), None, M, _st()))
     assert (o16b.float() - F.layer_norm(xb16.float(), (512,), gamma, beta, 1e-5)).abs().max() < 0.05
     res16 = torch.randn(M, 512, device="cuda", generator=g).bfloat16()
     acc = res16.clone()                       # residual aliases the output, like the engine's x = LN(x + s)
-    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, acc.data_ptr(), gamma.data_ptr(), beta.data_ptr(), None, acc.data_ptr(), M, _st()))
+    _lib.check(L.pt_layernorm512(xb16.data_ptr(), 0, acc.data_ptr(), None, gamma.data_ptr(), beta.data_ptr(), None, acc.data_ptr(), None, M, _st()))
     assert (acc.float() - F.layer_norm(xb16.float() + res16.float(), (512,), gamma, beta, 1e-5)).abs().max() < 0.05
     ref = F.layer_norm(x, (512,), gamma, beta, 1e-5)
     assert (o32 - ref).abs().max() < 2e-5 and (o16.float() - ref).abs().max() < 0.05
@@ -180,7 +180,7 @@ def test_layernorm_kernels_and_embed():
     xb = x.bfloat16()
     out = torch.zeros(M, 512, device="cuda", dtype=torch.bfloat16)
     _lib.check(L.pt_ln_mod_silu512(xb.data_ptr(), 0, gamma.data_ptr(), beta.data_ptr(), mod.data_ptr(), labels.data_ptr(), 8,
-                                   out.data_ptr(), M, _st()))
+                                   out.data_ptr(), None, M, _st()))
     m = mod[labels.long()].repeat_interleave(8, 0)
     y = F.layer_norm(xb.float(), (512,), gamma, beta, 1e-5) * (1 + m[:, :512]) + m[:, 512:]
     assert (out.float() - F.silu(y)).abs().max() < 0.06
@@ -190,10 +190,25 @@ def test_layernorm_kernels_and_embed():
     tok = torch.randint(0, 129, (M // N * N,), device="cuda", generator=g, dtype=torch.int32)
     e32 = torch.zeros(tok.numel(), 512, device="cuda")
     bad = torch.zeros(1, device="cuda", dtype=torch.int32)
-    _lib.check(L.pt_embed_tokens512(tok.data_ptr(), emb.data_ptr(), 129, pe.data_ptr(), N, e32.data_ptr(), None, tok.numel(),
-                                    bad.data_ptr(), _st()))
+    eh, el = torch.zeros_like(e32, dtype=torch.bfloat16), torch.zeros_like(e32, dtype=torch.bfloat16)
+    _lib.check(L.pt_embed_tokens512(tok.data_ptr(), emb.data_ptr(), 129, pe.data_ptr(), N, e32.data_ptr(), eh.data_ptr(),
+                                    el.data_ptr(), tok.numel(), bad.data_ptr(), _st()))
     ref = (emb[tok.long()].double() + pe.repeat(tok.numel() // N, 1)).float()
     assert torch.equal(e32, ref) and int(bad) == 0
+    # split-bf16 pair: hi = bf16(v), lo = bf16(v - hi); hi + lo carries 16 mantissa bits
+    assert torch.equal(eh, ref.bfloat16()) and torch.equal(el, (ref - ref.bfloat16().float()).bfloat16())
+    assert ((eh.float() + el.float()) - ref).abs().max() <= ref.abs().max() * 2.0 ** -16
+    # split outputs / residual of the LayerNorm kernels (the tolerance-tight mode): fp32 in, (hi, lo) residual and out
+    rh, rl = res16, (torch.randn(M, 512, device="cuda", generator=g) * 2.0 ** -9).bfloat16()
+    oh, ol = torch.zeros_like(o16), torch.zeros_like(o16)
+    _lib.check(L.pt_layernorm512(x.data_ptr(), 1, rh.data_ptr(), rl.data_ptr(), gamma.data_ptr(), beta.data_ptr(), None,
+                                 oh.data_ptr(), ol.data_ptr(), M, _st()))
+    ref = F.layer_norm(x + rh.float() + rl.float(), (512,), gamma, beta, 1e-5)
+    assert ((oh.float() + ol.float()) - ref).abs().max() <= 2.0 ** -16 * ref.abs().max()       # 16 mantissa bits
+    _lib.check(L.pt_ln_mod_silu512(x.data_ptr(), 1, gamma.data_ptr(), beta.data_ptr(), mod.data_ptr(), labels.data_ptr(), 8,
+                                   oh.data_ptr(), ol.data_ptr(), M, _st()))
+    y = F.layer_norm(x, (512,), gamma, beta, 1e-5) * (1 + m[:, :512]) + m[:, 512:]
+    assert ((oh.float() + ol.float()) - F.silu(y)).abs().max() <= 2.0 ** -15 * F.silu(y).abs().max()
 
 
 def test_pack_and_blend_match_torch():
@@ -207,7 +222,7 @@ def test_pack_and_blend_match_torch():
     H, Cp = 1, 384
     Tp = T + 2
     dst = torch.zeros(B, Tp, Cp, device="cuda", dtype=torch.bfloat16)
-    _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), Tpred, dst.data_ptr(), B, Cc, T, Tp, H, Cp, 0, 2, _st()))
+    _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), Tpred, dst.data_ptr(), None, B, Cc, T, Tp, H, Cp, 0, 2, _st()))
     interp = F.interpolate(pred, size=T, mode="linear")
     ref = src * mask + interp * (1 - mask)
     got = dst[:, H:H + T, :Cc].float().transpose(1, 2)
@@ -234,10 +249,13 @@ def test_pack_and_blend_same_length_paths(B, Cc, T):
     Tp = T + 5
     for mode, ref in ((0, src), (1, src * mask), (2, src * mask + pred * (1 - mask))):
         dst = torch.zeros(B, Tp, Cp, device="cuda", dtype=torch.bfloat16)
-        _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, dst.data_ptr(), B, Cc, T, Tp, H, Cp,
-                                  c_off, mode, _st()))
+        lo = torch.zeros_like(dst)
+        _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, dst.data_ptr(), lo.data_ptr(), B, Cc, T,
+                                  Tp, H, Cp, c_off, mode, _st()))
         got = dst[:, H:H + T, c_off:c_off + Cc].float().transpose(1, 2)
         assert torch.equal(got, ref.bfloat16().float())
+        got_lo = lo[:, H:H + T, c_off:c_off + Cc].float().transpose(1, 2)
+        assert torch.equal(got_lo, (ref - ref.bfloat16().float()).bfloat16().float())      # the split pair's lo plane
         chk = dst.clone()
         chk[:, H:H + T, c_off:c_off + Cc] = 0
         assert float(chk.abs().max()) == 0                  # halo rows and padding channels untouched

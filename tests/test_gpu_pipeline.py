@@ -1,14 +1,15 @@
-"""PQ-VAE / predictor / refiner CUDA plans vs the oracle and the reference-generated golden vectors.
+"""PQ-VAE / predictor / refiner CUDA plans (bf16 arithmetic) vs the oracle and the reference-generated golden vectors.
 
-Arithmetic type: bf16 tensor-core operands, fp32 accumulation, bf16 activations between layers (the reference
-is fp32).  Stated tolerances (normalised pose units, decoder output rms ~0.5, refiner output rms ~0.9):
-    PQ-VAE decode from identical codes      max-abs <= 0.04   mean-abs <= 0.006    (observed 0.012 / 0.002)
-    predictor poses from identical codes    max-abs <= 0.04                        (observed 0.011)
-    teacher-forced logits                   max-abs <= 0.12   rms <= 0.02          (observed 0.035 / 0.007)
-    refiner output                          max-abs <= 0.08   mean-abs <= 0.012    (observed 0.022 / 0.003)
-    per-joint (6-D block) mean error        <= 0.02
-PQ codes emitted from the CUDA encoder's own z are index-exact w.r.t. that z; against the fp32 reference's codes
-they may differ where the bf16 encoder error exceeds the top-2 gap (reported, bounded below)."""
+Arithmetic type: bf16 tensor-core operands, fp32 accumulation, bf16 activations between layers (the reference is fp32);
+the PQ-VAE ENCODER always runs in split-bf16 ("bf16x3") arithmetic, so z and the PQ codes are fp32-grade in either mode.
+Stated tolerance of the bf16 path (normalised pose units; decoder output rms ~0.5, refiner ~0.9, logits ~0.65) = 1.5 x the
+largest error observed on B200 over this file and tests/test_gpu_windows.py (profiles/r02_parity.md):
+    PQ-VAE decode / predictor poses, identical codes   max-abs <= 0.021   mean-abs <= 0.0030   (observed 0.0135 / 0.00195)
+    teacher-forced logits                               max-abs <= 0.035   mean-abs <= 0.0063   (observed 0.0232 / 0.00417)
+    refiner output (single window and window loops)     max-abs <= 0.038   mean-abs <= 0.0058   (observed 0.0250 / 0.00386)
+    predictor condition (AudEnc + context encoder)      max-abs <= 0.12    mean-abs <= 0.0063   (observed 0.0776 / 0.00417)
+    per-joint (6-D block) mean error                    <= 0.02
+The tolerance-tight mode (max-abs <= 1e-3, mean <= 1e-4; observed 5e-5 / 1e-5) is tests/test_gpu_precise.py."""
 import os
 
 import pytest
@@ -45,6 +46,25 @@ def noise(T, B, N, seed):
     return u, gum
 
 
+# Asserted bounds (max-abs, mean-abs) of the bf16 path per quantity = 1.5 x the largest error observed on B200 over the
+# tests of this file (printed with -s; profiles/r02_parity.md keeps the observations).  DESIGN.md section 4 states them.
+BOUND = {
+    "decode": (0.021, 0.0030),    # PQ-VAE decoder output, identical codes          (observed 0.0135 / 0.00195)
+    "logits": (0.035, 0.0063),    # teacher-forced logits                           (observed 0.0232 / 0.00417)
+    "refiner": (0.038, 0.0058),   # refiner output                                  (observed 0.0250 / 0.00386)
+    "cond": (0.12, 0.0063),       # predictor condition (AudEnc + context encoder)  (observed 0.0776 / 0.00417)
+}
+
+
+def _check(name, key, a, b):
+    """Assert the bf16 bound of `key`; prints the observation so the bound can be audited (-s)."""
+    e = (a - b).abs()
+    mx, mean = e.max().item(), e.mean().item()
+    print("[bf16 observed] %-40s max %.4f  mean %.5f  (ref rms %.3f)  bound %s"
+          % (name, mx, mean, b.pow(2).mean().sqrt().item(), BOUND[key]))
+    assert mx < BOUND[key][0] and mean < BOUND[key][1], (name, mx, mean, BOUND[key])
+
+
 def per_joint_error(a, b):
     """mean over joints of the L2 error of each 6-D rotation block (46 joints = jaw + 15 body + 30 hands)."""
     d = (a - b)[:, :276].reshape(a.shape[0], 46, 6, -1)
@@ -60,7 +80,8 @@ def test_cfg1_vqvae_golden(gold, states, weights):
     codes = enc.run(x.cuda()).cpu()
     z = enc.z_channel_first().cpu()
     assert z.shape == c["z"].shape
-    assert (z - c["z"]).abs().max() < 0.2 and (z - c["z"]).pow(2).mean().sqrt() < 0.03
+    # the encoder always runs in split-bf16 arithmetic: z is fp32-grade (tests/test_gpu_precise.py holds the tight checks)
+    assert (z - c["z"]).abs().max() < 1.5e-4 * c["z"].abs().max()
     # index-exact with respect to the z the encoder produced
     cbs = O.pq_codebooks(states[0])
     self_ref = O.pq_search(z, cbs)
@@ -74,12 +95,11 @@ def test_cfg1_vqvae_golden(gold, states, weights):
     dz = (z - c["z"]).permute(0, 2, 1).reshape(1, -1, 4, 128).norm(dim=-1)          # per (step, group) |dz|
     cmax = max(cb.norm(dim=1).max().item() for cb in cbs)
     assert bool((gap_ref[diff] <= 4.0 * dz[diff] * cmax + 1e-4).all())
-    assert diff.float().mean() < 0.1
+    assert diff.float().mean() <= 0.001
     # decode the REFERENCE codes: tolerance-matched poses
     rec = E.DecoderPlan(weights[0], 1, enc.Tq).run(codes=ref_codes.cuda()).cpu()
     assert rec.shape == c["recon"].shape == (1, 376, 296)
-    err = (rec - c["recon"]).abs()
-    assert err.max() < 0.04 and err.mean() < 0.006
+    _check("cfg1 decode of reference codes", "decode", rec, c["recon"])
     assert per_joint_error(rec, c["recon"]) < 0.02
 
 
@@ -93,11 +113,11 @@ def test_vqvae_shapes_vs_oracle(states, weights, B, T):
     codes = enc.run(x.cuda()).cpu()
     assert codes.shape == idx_ref.shape
     z = enc.z_channel_first().cpu()
-    assert (z - z_ref).abs().max() < 0.25
-    assert (codes == idx_ref).float().mean() > 0.85
+    assert (z - z_ref).abs().max() < 1.5e-4 * z_ref.abs().max()
+    assert (codes == idx_ref).float().mean() >= 0.999
     rec = E.DecoderPlan(weights[0], B, enc.Tq).run(codes=idx_ref.cuda()).cpu()
     assert rec.shape == rec_ref.shape
-    assert (rec - rec_ref).abs().max() < 0.04
+    _check("decode B=%d T=%d" % (B, T), "decode", rec, rec_ref)
 
 
 def test_decode_from_latents_matches_decode_from_codes(states, weights):
@@ -107,7 +127,11 @@ def test_decode_from_latents_matches_decode_from_codes(states, weights):
     a = E.DecoderPlan(weights[0], 2, 22).run(codes=codes.cuda()).clone()
     lat = O.pq_gather(codes, O.pq_codebooks(states[0])).transpose(1, 2).contiguous()
     b = E.DecoderPlan(weights[0], 2, 22, from_latents=True).run(latents=lat.cuda())
-    assert torch.equal(a, b)
+    # codes enter through the fused gather + aft_vq_conv table (fp32 sums), latents through a bf16 GEMM: same function
+    # within the bf16 decoder tolerance, both against the oracle
+    ref = O.decoder_sc(lat, states[0])
+    _check("decode from codes (fused table)", "decode", a.cpu(), ref)
+    _check("decode from latents (GEMM)", "decode", b.cpu(), ref)
 
 
 def test_cfg3_logits_golden(gold, states, weights):
@@ -126,8 +150,27 @@ def test_cfg3_logits_golden(gold, states, weights):
     plan.cur.copy_(tokens.view(3, -1))
     plan.plan_iter.run()
     logits = plan.logits.view(3, 22, 4, 128).cpu()
-    err = logits - c["logits"]
-    assert err.abs().max() < 0.12 and err.pow(2).mean().sqrt() < 0.02
+    _check("cfg3 logits (B=3)", "logits", logits, c["logits"])
+
+
+def test_cfg3_predictor_forward_b64_vs_oracle(states, weights):
+    """BASELINE config 3 at its own batch: audio [64, 768, 180] ~ N(0, 1), gt zeros, mask zeros, id in {0..3}; one
+    PredictorNet forward = context encoder + one tokens_to_logits pass on the all-MASK token grid, vs the oracle."""
+    from probtalk_b200 import engine as E
+    B, T = 64, 180
+    aud = S.synthetic_audio(B, T, 1003 + 64)
+    gt, mask = torch.zeros(B, 376, T), torch.zeros(B, 1, T)
+    labels = torch.arange(B) % 4
+    plan = E.PredictorPlan(weights[1], weights[0], B, T)
+    plan.aud.copy_(aud); plan.gt.copy_(gt); plan.mask.copy_(mask); plan.labels.copy_(labels.int())
+    plan.run_condition()
+    plan.cur.fill_(E.MASK_ID)
+    plan.plan_iter.run()
+    _, cond_ref = O.predictor_condition(aud, gt, mask, states[1])
+    tokens = torch.full((B, 22, 4), E.MASK_ID, dtype=torch.int32)
+    ref = O.tokens_to_logits(tokens, labels, cond_ref, O._sub(states[1]["Predictor"], "decoder"))
+    _check("cfg3 condition (B=64)", "cond", plan.cond.valid().float().transpose(1, 2).cpu(), cond_ref)
+    _check("cfg3 logits (B=64)", "logits", plan.logits.view(B, 22, 4, 128).cpu(), ref)
 
 
 def test_context_encoder_vs_oracle(states, weights):
@@ -141,7 +184,7 @@ def test_context_encoder_vs_oracle(states, weights):
     plan.run_condition()
     _, cond_ref = O.predictor_condition(aud, gt, mask, states[1])
     cond = plan.cond.valid().float().transpose(1, 2).cpu()
-    assert (cond - cond_ref).abs().max() < 0.2 and (cond - cond_ref).pow(2).mean().sqrt() < 0.02
+    _check("predictor condition", "cond", cond, cond_ref)
 
 
 @pytest.mark.parametrize("step", [0, 2, 5, 7])
@@ -192,17 +235,16 @@ def test_cfg4_predictor_refiner_golden(gold, states, weights):
     assert torch.equal(poses[:, :, :30], gt[:, :, :30])
     # identical codes -> tolerance-matched poses
     tf = O.predictor_decode(codes.long(), gt * mask, mask, vq, T)
-    assert (poses - tf).abs().max() < 0.04
+    _check("cfg4 predictor poses, same codes", "decode", poses, tf)
     # the reference's codes through our decoder reproduce the reference's poses
     plan.cur.copy_(c["codes"].int().view(B, -1))
     ours_on_ref_codes = plan.run_decode().cpu()
-    assert (ours_on_ref_codes - c["poses"]).abs().max() < 0.04
+    _check("cfg4 decode of reference codes", "decode", ours_on_ref_codes, c["poses"])
     assert per_joint_error(ours_on_ref_codes, c["poses"]) < 0.02
     # refiner on the reference's predictor output vs the reference's refiner output
     rp = E.RefinerPlan(weights[2], B, T, T)
     out = rp.run(aud.cuda(), gt.cuda(), mask.cuda(), c["poses"].cuda(), labels.int().cuda()).cpu()
-    err = (out - c["refined"]).abs()
-    assert err.max() < 0.08 and err.mean() < 0.012
+    _check("cfg4 refiner", "refiner", out, c["refined"])
     assert per_joint_error(out, c["refined"]) < 0.03
     assert torch.equal(out[:, :, :30], gt[:, :, :30])
 
@@ -218,7 +260,7 @@ def test_refiner_interpolates_shorter_prediction(states, weights):
     labels = torch.tensor([0, 3])
     out = E.RefinerPlan(weights[2], B, T, Tp).run(aud.cuda(), gt.cuda(), mask.cuda(), pred.cuda(), labels.int().cuda()).cpu()
     ref = O.refiner_infer_on_batch(aud, gt, mask, labels, pred, states[2]["HFTransformer"])
-    assert (out - ref).abs().max() < 0.08
+    _check("refiner 176 <- 144", "refiner", out, ref)
 
 
 def test_sampler_distribution_matches_oracle(states, weights):
@@ -279,7 +321,7 @@ def test_wrapper_api_roundtrip(states):
     assert lat.shape == (B, 512, 22)
     prelim = pred.VQ.decode(lat, None)                                    # demo.py:153
     ref_dec = O.decoder_sc(O.pq_gather(codes.cpu().long(), O.pq_codebooks(vq)).transpose(1, 2).contiguous(), vq)
-    assert (prelim.cpu() - ref_dec).abs().max() < 0.04
+    _check("wrapper VQ.decode(latents)", "decode", prelim.cpu(), ref_dec)
     # PQ-VAE wrapper (vq_teacher.infer_on_audio): encode -> quantise -> decode
     vqt = nets.s2g_body_vqt(args, _config())
     vqt.load_state_dict({"VQ": vq})

@@ -176,3 +176,35 @@ def test_predictor_and_refiner_infer_on_batch(states, ref_pred, ref_refiner):
     out = O.refiner_infer_on_batch(aud, gt, mask, torch.tensor([1]), poses, rst["HFTransformer"])
     assert out.shape == (B, 376, T)
     assert torch.allclose(out, ref_out, atol=1e-4, rtol=1e-4)
+
+
+def test_window_loops_match_reference_scripts(states, ref_pred, ref_refiner):
+    """oracle/window_oracle.py against LITERAL transcriptions of the script loops (scripts/test_holisticbody.py:239-262,
+    scripts/demo.py:116-181) driving the unmodified reference wrappers / All_In_One_Model.__call__, sampler noise
+    injected per window.  t = 300: windows of 180 and 150 frames (the second with 30 known frames of feedback)."""
+    from oracle import make_golden_windows as GW
+    from oracle import window_oracle as WO
+    vq, pst, rst = states
+    gen = GW.reference_generator(ref_pred, ref_refiner)
+    c = GW.EVAL
+    aud1, gt1, mask, noise = GW.eval_inputs()
+    with torch.no_grad():
+        ref = GW.ref_windows_eval(gen, aud1, aud1, gt1, mask, torch.tensor([c["id"]]), c["B"], noise)
+    B = c["B"]
+    ids = torch.tensor([c["id"]]).repeat(B)
+    out, codes = WO.windows_eval(aud1.repeat(B, 1, 1), gt1.repeat(B, 1, 1), mask, ids, pst, vq, rst["HFTransformer"], noise=noise)
+    assert out.shape == ref.shape == (B, 376, c["t"])
+    assert [tuple(x.shape) for x in codes] == [(B, 22, 4), (B, 18, 4)]
+    assert torch.allclose(out, ref, atol=2e-4, rtol=1e-4)
+    assert torch.equal(out[:, :, c["known"][0]:c["known"][1]], gt1.repeat(B, 1, 1)[:, :, c["known"][0]:c["known"][1]])
+    # teacher-forcing the codes reproduces the same poses (what the GPU parity test relies on)
+    out_tf, _ = WO.windows_eval(aud1.repeat(B, 1, 1), gt1.repeat(B, 1, 1), mask, ids, pst, vq, rst["HFTransformer"], codes=codes)
+    assert torch.equal(out_tf, out)
+    d = GW.DEMO
+    aud1, noise = GW.demo_inputs()
+    with torch.no_grad():
+        ref_poses, ref_codes, _ = GW.ref_windows_demo(gen, aud1, torch.tensor([d["id"]]), d["B"], noise)
+    ids = torch.tensor([d["id"]]).repeat(d["B"])
+    poses, all_codes, _ = WO.windows_demo(aud1.repeat(d["B"], 1, 1), ids, pst, vq, rst["HFTransformer"], noise=noise)
+    assert torch.equal(all_codes.long(), ref_codes.long()) and all_codes.shape == (d["B"], 22 + 18 - 3, 4)
+    assert torch.allclose(poses, ref_poses, atol=2e-4, rtol=1e-4)

@@ -33,7 +33,7 @@ def timeit(name, fn, byts):
 
 n = B * C_ * T
 for mode in (0, 1, 2):
-    timeit("pack_rows mode %d" % mode, lambda: _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, dst.data_ptr(), B, C_, T, T + 8, 4, 384, 0, mode, st)),
+    timeit("pack_rows mode %d" % mode, lambda: _lib.check(L.pt_pack_rows(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, dst.data_ptr(), None, B, C_, T, T + 8, 4, 384, 0, mode, st)),
            n * 4 * (2 if mode == 2 else 1) + n * 2)
 timeit("interp_blend pow 1", lambda: _lib.check(L.pt_interp_blend(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), T, out.data_ptr(), B, C_, T, 1, st)), n * 12)
 timeit("interp_blend pow 2 (Tpred 176)", lambda: _lib.check(L.pt_interp_blend(src.data_ptr(), mask.data_ptr(), pred.data_ptr(), 176, out.data_ptr(), B, C_, T, 2, st)), n * 12)
