@@ -2,9 +2,10 @@
 
 This module is TEST INFRASTRUCTURE.  It exists to pin ``oracle/probtalk_oracle.py``
 against the real reference and to generate the committed golden vectors in
-``tests/golden/``.  It imports ``/root/reference`` (read-only, present only in the
-authoring container -- NOT on the GPU box), so nothing on the product path, in the
-``-m gpu`` tests, in ``smoke()`` or in ``bench.py`` may import it.
+``tests/golden/``, and to run the reference arm of ``bench.py`` (``--impl reference`` / ``cpu_baseline``).  It imports
+``/root/reference`` (read-only, present only in the authoring container) or, on the GPU box, the unmodified snapshot
+``oracle/_ref/reference`` made by ``oracle/build_ref.py``; nothing on the product path, in the ``-m gpu`` tests or in
+``smoke()`` may import it.
 
 The reference hard-codes CUDA devices, needs a handful of absent third-party modules
 at import time and breaks on torch >= 2.0; the shims below (none of which edit the
@@ -28,7 +29,10 @@ import types
 
 import torch
 
+_SNAPSHOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "reference")     # oracle/build_ref.py
 REFERENCE_ROOT = os.environ.get("PROBTALK_REFERENCE", "/root/reference")
+if not os.path.isdir(os.path.join(REFERENCE_ROOT, "nets")) and os.path.isdir(os.path.join(_SNAPSHOT, "nets")):
+    REFERENCE_ROOT = _SNAPSHOT            # the GPU box: the unmodified snapshot that travelled with the repository
 
 
 def reference_available() -> bool:

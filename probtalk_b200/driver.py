@@ -77,6 +77,16 @@ class HolisticPipeline:
         self._pred, self._ref, self._dec = E.PlanCache(), E.PlanCache(), E.PlanCache(4)
         self.generator = None          # torch.Generator for the sampler noise (None = global CUDA RNG)
 
+    @classmethod
+    def from_weights(cls, VW, PW, RW):
+        """A pipeline over already-prepared weights (engine.VQVAEWeights / PredictorWeights / RefinerWeights)."""
+        self = cls.__new__(cls)
+        self.device, self.precision = torch.device(PW.device), PW.precision
+        self.VW, self.PW, self.RW = VW, PW, RW
+        self._pred, self._ref, self._dec = E.PlanCache(), E.PlanCache(), E.PlanCache(4)
+        self.generator = None
+        return self
+
     def predictor(self, B, T):
         return self._pred.get((B, T), lambda: E.PredictorPlan(self.PW, self.VW, B, T))
 

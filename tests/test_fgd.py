@@ -96,3 +96,37 @@ def test_evaluator_single_chunk_push_does_not_alias(gold):
         fg = plan.extract(gold["gene"][i:i + 1].cuda()).clone()
         assert torch.equal(ev.real_feat[i], fr.t()) and torch.equal(ev.gene_feat[i], fg.t())
         assert not torch.equal(ev.real_feat[i], ev.gene_feat[i])
+
+
+METRICS_GOLD = os.path.join(os.path.dirname(__file__), "golden", "metrics_vectors.pt")
+
+
+def test_oracle_lvd_diversity_match_reference_golden():
+    from oracle.make_golden_metrics import make_inputs
+    for c in torch.load(METRICS_GOLD, weights_only=False)["cases"]:
+        gt, pr = make_inputs(c["seed"], *c["shape"])
+        B, T, J, D = c["shape"]
+        assert abs(FO.lvd(gt, pr) - c["lvd"]) <= 1e-6 * max(1.0, abs(c["lvd"]))
+        assert abs(FO.lvd(gt, pr[0]) - c["lvd_single"]) <= 1e-6 * max(1.0, abs(c["lvd_single"]))
+        assert abs(FO.diversity(pr.reshape(B, T, J * D).numpy()) - c["diversity"]) <= 1e-6 * max(1.0, c["diversity"])
+
+
+@pytest.mark.gpu
+def test_lvd_diversity_kernels_vs_reference_golden():
+    """pt_lvd / pt_diversity (fp32 differences and norms, fp64 sums) against the reference's own numbers."""
+    from oracle.make_golden_metrics import make_inputs
+    from probtalk_b200 import evaluation as EV
+    for c in torch.load(METRICS_GOLD, weights_only=False)["cases"]:
+        gt, pr = make_inputs(c["seed"], *c["shape"])
+        B, T, J, D = c["shape"]
+        v, per = EV.lvd(gt.cuda(), pr.cuda())
+        assert abs(v - c["lvd"]) <= 2e-6 * max(1.0, abs(c["lvd"])) and per.shape == (B,)
+        v1, _ = EV.lvd(gt.cuda(), pr[0].cuda())
+        assert abs(v1 - c["lvd_single"]) <= 2e-6 * max(1.0, abs(c["lvd_single"]))
+        d, pairs = EV.diversity(pr.reshape(B, T, J * D).cuda())
+        assert abs(d - c["diversity"]) <= 2e-6 * max(1.0, c["diversity"]) and pairs.numel() == B * (B - 1) // 2
+        d2, pairs2 = EV.diversity(pr.reshape(B, T, J * D).cuda())
+        assert d == d2 and torch.equal(pairs, pairs2)              # deterministic reduction order
+    from probtalk_b200 import _lib
+    with pytest.raises(_lib.PtError):
+        EV.diversity(torch.zeros(1, 10, 3).cuda())

@@ -332,57 +332,95 @@ def test_wrapper_api_roundtrip(states):
     assert qo.quantized.shape == (2, 512, 9) and qo.loss.shape == (2, 9, 4)
 
 
-def _frechet(a, b):
-    """Frechet distance between Gaussians fitted to two feature sets (formula of evaluation/FGD.py:200-257)."""
-    import numpy as np
-    from scipy import linalg
-    mu1, mu2 = a.mean(0), b.mean(0)
-    s1, s2 = np.cov(a, rowvar=False), np.cov(b, rowvar=False)
-    covmean = np.asarray(linalg.sqrtm(s1.dot(s2)))
-    if not np.isfinite(covmean).all():
-        off = np.eye(s1.shape[0]) * 1e-6
-        covmean = np.asarray(linalg.sqrtm((s1 + off).dot(s2 + off)))
-    covmean = covmean.real
-    d = mu1 - mu2
-    return float(d.dot(d) + np.trace(s1) + np.trace(s2) - 2 * np.trace(covmean))
+# ---------------------------------------------------------------------------------------------------------------------
+# north_star: "FGD / diversity on identical inputs must be unchanged".  The trained FGD feature extractor
+# (experiments/val_models/*.pth) is not available, so features come from the fixed-seed EmbeddingNet of
+# tests/golden/fgd_vectors.pt (SURVEY.md 8c caveat 3) -- run by the in-tree EmbeddingPlan / feature_stats / frechet_distance
+# (probtalk_b200.evaluation), LVD and diversity by pt_lvd / pt_diversity.  32 clips x 16 samples = 512 free-running
+# predictor + refiner windows = 1024 90-frame chunks per set.  Three sets: the CUDA path with noise A, the oracle with the
+# same noise A, and the oracle with independent noise B -- the oracle-vs-oracle differences are the yardstick.
+N_CLIPS, N_SAMPLES = 32, 16
 
 
-def _diversity(poses):
-    """mean pairwise L1 distance between the samples generated for one clip (evaluation/metrics.py:96-110)."""
-    B = poses.shape[0]
-    flat = poses.reshape(B, -1)
-    d = (flat[:, None] - flat[None]).abs().mean(-1)
-    return float(d.sum() / (B * (B - 1)))
+def _metric_inputs():
+    B, T = N_CLIPS * N_SAMPLES, 180
+    aud = S.synthetic_audio(N_CLIPS, T, 301).repeat_interleave(N_SAMPLES, 0)
+    labels = (torch.arange(N_CLIPS) % 4).repeat_interleave(N_SAMPLES)
+    return aud, torch.zeros(B, 376, T), torch.zeros(B, 1, T), labels
 
 
-def test_fgd_and_diversity_unchanged(states, weights):
-    """north_star: 'FGD / diversity on identical inputs must be unchanged'.  The trained FGD feature extractor
-    (experiments/val_models/*.pth) is not available, so features come from a fixed-seed random conv embedding
-    (SURVEY.md 8c caveat 3).  16 samples of one clip from the CUDA predictor vs 16 from the oracle with the same
-    injected noise, and vs a second oracle run with different noise as the yardstick."""
-    import torch.nn.functional as F
-    from probtalk_b200 import engine as E
+@pytest.fixture(scope="module")
+def oracle_sets(states):
     vq, pst, rst = states
-    B, T = 16, 180
-    aud = S.synthetic_audio(1, T, 301).repeat(B, 1, 1)
-    gt = torch.zeros(B, 376, T)
-    mask = torch.zeros(B, 1, T)
-    labels = torch.full((B,), 2)
+    aud, gt, mask, labels = _metric_inputs()
+    sets = []
+    for seed in (302, 303):
+        u, gum = noise(8, aud.shape[0], 88, seed)
+        outs, codes = [], []
+        for i in range(0, aud.shape[0], 64):                      # oracle in slices of 64 (memory)
+            sl = slice(i, i + 64)
+            p, c = O.predictor_infer_on_batch(aud[sl], gt[sl], mask[sl], labels[sl], pst, vq, u[:, sl], gum[:, sl])
+            outs.append(O.refiner_infer_on_batch(aud[sl], gt[sl], mask[sl], labels[sl], p, rst["HFTransformer"]))
+            codes.append(c)
+        sets.append((torch.cat(outs), torch.cat(codes)))
+    return sets
+
+
+def _chunks90(p):
+    """[N, 376, T] -> [N * (T // 90), 376, 90]: the reference's transpose(1, 2).unfold(1, 90, 90).flatten(0, 1)
+    (scripts/test_holisticbody.py:279)."""
+    return p.transpose(1, 2).unfold(1, 90, 90).flatten(0, 1).contiguous()
+
+
+@pytest.mark.parametrize("precision", ["bf16", "bf16x3"])
+def test_fgd_lvd_diversity_unchanged(states, oracle_sets, precision):
+    from probtalk_b200 import driver as D, engine as E, evaluation as EV
+    fg = torch.load(os.path.join(os.path.dirname(__file__), "golden", "fgd_vectors.pt"), weights_only=False)
+    emb = E.EmbeddingPlan(E.EmbeddingWeights(fg["state_dict"], "cuda", precision="bf16x3"), 128)
+    pipe = D.HolisticPipeline(*states, "cuda", precision=precision)
+    aud, gt, mask, labels = _metric_inputs()
+    B = aud.shape[0]
     u, gum = noise(8, B, 88, 302)
-    plan = E.PredictorPlan(weights[1], weights[0], B, T)
-    gpu, _ = plan.run(aud.cuda(), gt.cuda(), mask.cuda(), labels.int().cuda(), noise=(u.cuda(), gum.cuda()))
-    gpu = gpu.cpu()
-    ora, _ = O.predictor_infer_on_batch(aud, gt, mask, labels, pst, vq, u, gum)
-    u2, gum2 = noise(8, B, 88, 303)
-    ora2, _ = O.predictor_infer_on_batch(aud, gt, mask, labels, pst, vq, u2, gum2)
-    g = torch.Generator().manual_seed(0)
-    w = torch.randn(32, 376, 15, generator=g) / (376 * 15) ** 0.5
+    gpu, codes = pipe.window(aud.cuda(), gt.cuda(), mask.cuda(), labels.int().cuda(), noise=(u.cuda(), gum.cuda()))
+    gpu, codes = gpu.clone(), codes.cpu().long()
+    (ora, ora_codes), (ora2, _) = oracle_sets
+    agree = (codes == ora_codes.long()).float().mean().item()
+    real = S.synthetic_poses(B, 180, 304)                              # a fixed "real" set for FGD(generated, real)
 
     def feats(p):
-        return torch.tanh(F.conv1d(p, w, stride=5)).permute(0, 2, 1).reshape(-1, 32).double().numpy()
+        c = _chunks90(p.cuda().float())
+        return torch.cat([emb.extract(c[i:i + 128]).clone() for i in range(0, c.shape[0], 128)])
 
-    fd_same = _frechet(feats(gpu), feats(ora))          # CUDA vs oracle, same noise
-    fd_yard = _frechet(feats(ora2), feats(ora))         # oracle vs oracle, different noise
-    assert fd_same <= 1.5 * fd_yard + 1e-3, (fd_same, fd_yard)
-    dv_gpu, dv_ora, dv_ora2 = _diversity(gpu), _diversity(ora), _diversity(ora2)
-    assert abs(dv_gpu - dv_ora) <= max(0.1 * dv_ora, 2 * abs(dv_ora2 - dv_ora)), (dv_gpu, dv_ora, dv_ora2)
+    def fgd(fa, fb):
+        (ma, sa), (mb, sb) = EV.feature_stats(fa), EV.feature_stats(fb)
+        return EV.frechet_distance(ma.cpu().numpy(), sa.cpu().numpy(), mb.cpu().numpy(), sb.cpu().numpy())
+
+    f_gpu, f_ora, f_ora2, f_real = feats(gpu), feats(ora), feats(ora2), feats(real)
+    assert f_gpu.shape == (2 * B, 128)
+    fd_same, fd_yard = fgd(f_gpu, f_ora), fgd(f_ora2, f_ora)          # same noise: CUDA vs oracle; yardstick: oracle vs oracle
+    g_gpu, g_ora, g_ora2 = fgd(f_gpu, f_real), fgd(f_ora, f_real), fgd(f_ora2, f_real)
+
+    def per_clip(fn, p):
+        p = p.cuda().float()
+        return sum(fn(p[c * N_SAMPLES:(c + 1) * N_SAMPLES]) for c in range(N_CLIPS)) / N_CLIPS
+
+    div = lambda p: per_clip(lambda x: EV.diversity(x.transpose(1, 2))[0], p)                     # [16, 180, 376]
+    kp = lambda x: x[:, :276].transpose(1, 2).reshape(x.shape[0], 180, 46, 6)                     # 46 joints x 6-D
+    realc = real.cuda()
+    lvd = lambda p: sum(EV.lvd(kp(realc[c * N_SAMPLES:c * N_SAMPLES + 1])[0], kp(p.cuda().float()[c * N_SAMPLES:(c + 1) * N_SAMPLES]))[0]
+                        for c in range(N_CLIPS)) / N_CLIPS
+    d_gpu, d_ora, d_ora2 = div(gpu), div(ora), div(ora2)
+    l_gpu, l_ora, l_ora2 = lvd(gpu), lvd(ora), lvd(ora2)
+    print("[%s] code agreement %.4f | FGD(cuda, oracle same noise) %.4f vs yardstick FGD(oracle B, oracle A) %.4f | "
+          "FGD vs real: cuda %.3f oracle %.3f oracle-B %.3f | diversity %.5f / %.5f / %.5f | LVD %.4f / %.4f / %.4f"
+          % (precision, agree, fd_same, fd_yard, g_gpu, g_ora, g_ora2, d_gpu, d_ora, d_ora2, l_gpu, l_ora, l_ora2))
+    # unchanged = closer to the oracle than a second oracle run with other noise is
+    assert fd_same <= fd_yard + 1e-6, (fd_same, fd_yard)
+    assert abs(g_gpu - g_ora) <= max(1.5 * abs(g_ora2 - g_ora), 0.01 * g_ora), (g_gpu, g_ora, g_ora2)
+    assert abs(d_gpu - d_ora) <= max(1.5 * abs(d_ora2 - d_ora), 0.01 * d_ora), (d_gpu, d_ora, d_ora2)
+    assert abs(l_gpu - l_ora) <= max(1.5 * abs(l_ora2 - l_ora), 0.01 * l_ora), (l_gpu, l_ora, l_ora2)
+    if precision == "bf16x3":
+        # fp32-grade logits: the sampler takes the oracle's decisions, so the metrics coincide, not just "stay close"
+        assert agree >= 0.995
+        assert fd_same <= 0.02 * fd_yard and abs(g_gpu - g_ora) <= 1e-3 * g_ora
+        assert abs(d_gpu - d_ora) <= 1e-3 * d_ora and abs(l_gpu - l_ora) <= 1e-3 * l_ora
