@@ -38,7 +38,10 @@ const char* pt_last_error(void);
  *   gap_out    fp32  [B, W, G] or NULL: distance gap between the best and the second-best code
  *   score_dump fp32  [B, W, G, K] or NULL (test hook: the tensor-core scores |c|^2 - 2 x.c)
  *   n_rescored int32 [1] or NULL (test hook: incremented once per row decided by fp32 re-scoring)
- * Only K = D = 128 (config/vq.json) is built. */
+ * Shapes: D = 64 or 128, K a multiple of 16, G >= 1 -- config/vq.json's ProductQuantization (G = 4, K = D = 128) and
+ * the single-codebook VectorQuantizerEMA of nets/smplx_body_vq.py:48-53 (G = 1, D = 64, K = code_num = 2048).
+ * Codebooks with more than 128 codes are searched in chunks of 128 whose fp32 winners are merged through idx_out
+ * itself (packed atomicMin, unpacked before the call's work on the stream ends); gap_out must be NULL for K > 128. */
 int pt_pq_search(const float* z, long long zs_b, long long zs_c, long long zs_w, int B, int W, int G, int K, int D,
                  const float* codebooks, long long* idx_out, float* gap_out, float* score_dump, int* n_rescored,
                  void* stream);

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libprobtalk_b200.so")
+# PROBTALK_B200_LIB: developer override (A/B measurements of two builds inside one GPU call)
+LIB_PATH = os.environ.get("PROBTALK_B200_LIB") or os.path.join(_HERE, "lib", "libprobtalk_b200.so")
 
 _lib = None
 

@@ -24,20 +24,20 @@
 
 namespace {
 
-constexpr int kD = 128;          // sub-vector width
-constexpr int kK = 128;          // codes per sub-codebook
+constexpr int kK = 128;          // codes per staged codebook chunk (UMMA N); larger codebooks are split into chunks
 constexpr int kTileRows = 128;   // UMMA M
 constexpr int kLoadWarps = 4, kScanWarps = 4;
 constexpr int kThreads = (kLoadWarps + 1 + kScanWarps) * 32;   // 288: loaders, MMA issuer, scanners
-constexpr uint32_t kOpBytes = kTileRows * kD * 2;   // one bf16 operand tile: 32 KB (two 64-col swizzle atoms)
-constexpr uint32_t kAtomBytes = kTileRows * 128;    // 16 KB
+constexpr uint32_t kAtomBytes = kTileRows * 128;    // 16 KB: one 64-column SWIZZLE_128B atom of a 128-row operand tile
 constexpr float kBand = 2.5e-4f;                    // rigorous bound is ~9.3e-5 * |x||c| on the dot, x2 for the score
 
+template <int kD>                  // sub-vector width: 128 (ProductQuantization, vq.json) or 64 (VectorQuantizerEMA)
 struct PqSmem {
+  static constexpr uint32_t kOpBytes = kTileRows * kD * 2;   // one bf16 operand tile (kD / 64 swizzle atoms)
   uint8_t a_ops[2][kOpBytes];      // query tile hi | lo (each 1024-B aligned)
-  float stage[kTileRows * kD];     // raw fp32 rows of the NEXT tile, filled asynchronously with cp.async (64 KB)
-  uint8_t b_ops[2][kOpBytes];      // codebook hi | lo
-  float sc2[kK];                   // |c_j|^2 (fp32, deterministic order)
+  float stage[kTileRows * kD];     // raw fp32 rows of the NEXT tile, filled asynchronously with cp.async
+  uint8_t b_ops[2][kOpBytes];      // codebook chunk hi | lo
+  float sc2[kK];                   // |c_j|^2 (fp32, deterministic order); +inf for the padding rows of a short chunk
   float sx2[4][kTileRows];         // |x_r|^2, ring of 4 tiles (only used for the error band)
   float cmax_w[8];
   uint64_t a_full, a_empty, t_full[2], t_empty[2];
@@ -47,25 +47,16 @@ struct PqSmem {
 __device__ __forceinline__ void split_store(uint8_t* hi_tile, uint8_t* lo_tile, uint32_t off, const float (&v)[8]) {
   uint32_t h[4], l[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * i]), h1 = __float2bfloat16_rn(v[2 * i + 1]);
-    float r0 = v[2 * i] - __bfloat162float(h0), r1 = v[2 * i + 1] - __bfloat162float(h1);
-    __nv_bfloat162 hh; hh.x = h0; hh.y = h1;
-    h[i] = *reinterpret_cast<uint32_t*>(&hh);
-    l[i] = pt::pack_bf16x2(r0, r1);
-  }
+  for (int i = 0; i < 4; ++i) pt::split_bf16x2(v[2 * i], v[2 * i + 1], h[i], l[i]);
   *reinterpret_cast<uint4*>(hi_tile + off) = make_uint4(h[0], h[1], h[2], h[3]);
   *reinterpret_cast<uint4*>(lo_tile + off) = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// 4 consecutive fp32 -> hi / lo bf16 pairs at element k0 of row r (K-major SW128 tile of two 64-col atoms)
+// 4 consecutive fp32 -> hi / lo bf16 pairs at element k0 of row r (K-major SW128 tile of 64-column atoms)
 __device__ __forceinline__ void split_store4(uint8_t* hi_tile, uint8_t* lo_tile, int r, int k0, const float4& c) {
-  __nv_bfloat16 h0 = __float2bfloat16_rn(c.x), h1 = __float2bfloat16_rn(c.y), h2 = __float2bfloat16_rn(c.z),
-                h3 = __float2bfloat16_rn(c.w);
-  __nv_bfloat162 a0, a1; a0.x = h0; a0.y = h1; a1.x = h2; a1.y = h3;
-  const uint2 hi = make_uint2(*reinterpret_cast<uint32_t*>(&a0), *reinterpret_cast<uint32_t*>(&a1));
-  const uint2 lo = make_uint2(pt::pack_bf16x2(c.x - __bfloat162float(h0), c.y - __bfloat162float(h1)),
-                              pt::pack_bf16x2(c.z - __bfloat162float(h2), c.w - __bfloat162float(h3)));
+  uint2 hi, lo;
+  pt::split_bf16x2(c.x, c.y, hi.x, lo.x);
+  pt::split_bf16x2(c.z, c.w, hi.y, lo.y);
   const uint32_t off = (k0 >> 6) * kAtomBytes + pt::sw128_offset(r, (k0 & 63) >> 3) + (k0 & 7) * 2;
   *reinterpret_cast<uint2*>(hi_tile + off) = hi;
   *reinterpret_cast<uint2*>(lo_tile + off) = lo;
@@ -76,29 +67,59 @@ __device__ __forceinline__ float warp_sum(float v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// sum over the kLanes consecutive lanes that share a row (kLanes = 32 or 16)
+template <int kLanes>
+__device__ __forceinline__ float row_sum(float v) {
+#pragma unroll
+  for (int o = kLanes / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// order-preserving map fp32 -> uint32 (for atomicMin on packed (distance, index) words)
+__device__ __forceinline__ unsigned ordered_bits(float f) {
+  const unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
 
 struct PqArgs {
   const float* z;
   long long zs_b, zs_w, zs_c;   // element strides of z[b, c, w]
-  int B, W, G;
-  const float* codebooks;       // [G, 128, 128] fp32
+  int B, W, G, K;
+  const float* codebooks;       // [G, K, D] fp32
   long long* idx_out;           // [B*W, G]
   float* gap_out;               // [B*W, G] or null
-  float* score_dump;            // [B*W, G, 128] or null (test hook)
+  float* score_dump;            // [B*W, G, K] or null (test hook)
   int* n_rescored;              // single counter or null (test hook)
   int rows_per_tile, n_tiles, ctas_per_group;
+  int n_chunks;                 // ceil(K / 128): a CTA is bound to ONE (sub-codebook, chunk of 128 codes)
   int rows_fast;                // 1: channels-last rows, 16-byte aligned -> float4 row loader
 };
 
-template <bool kDump>
+// Codebooks with more than 128 codes (VectorQuantizerEMA, code_num = 2048): every chunk's CTAs find the chunk's fp32
+// winner for each row and fold it into idx_out with atomicMin on the packed word (ordered fp32 distance << 32 | index)
+// -- the global fp32 argmin is the minimum over the chunk argmins, equal distances resolve to the lower index like
+// torch.argmin.  idx_out is preset to ~0 before the launch and unpacked by this kernel afterwards.
+__global__ void pq_unpack_kernel(long long* __restrict__ idx, long long n) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i < n) idx[i] = (long long)(static_cast<unsigned long long>(idx[i]) & 0xffffffffull);
+}
+
+template <int kD, bool kDump>
 __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
+  using Smem = PqSmem<kD>;
+  constexpr int kRowLanes = kD / 4;                  // lanes that share one row in the float4 loaders (32 or 16)
+  constexpr int kRowsPerInstr = 32 / kRowLanes;      // rows one warp-wide float4 access covers (1 or 2)
   extern __shared__ uint8_t smem_raw[];
-  PqSmem& s = *reinterpret_cast<PqSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = blockIdx.x / a.ctas_per_group, part = blockIdx.x % a.ctas_per_group;
+  const int vg = blockIdx.x / a.ctas_per_group, part = blockIdx.x % a.ctas_per_group;
+  const int g = vg / a.n_chunks, chunk = vg - g * a.n_chunks;
+  const int code0 = chunk * kK;                      // first code of this CTA's chunk
+  const int n_codes = min(kK, a.K - code0);          // real codes in the chunk (the rest is padding)
+  const bool multi = a.n_chunks > 1;
   const long long total_rows = (long long)a.B * a.W;
-  const float* cb = a.codebooks + (size_t)g * kK * kD;
+  const float* cb = a.codebooks + ((size_t)g * a.K + code0) * kD;
   const int W = a.W;
+  const int sub_row = lane / kRowLanes, sub_col = (lane % kRowLanes) * 4;
 
   if (warp == kLoadWarps) {                       // the MMA warp also owns TMEM
     pt::tmem_alloc(&s.tmem_base, 256);
@@ -115,11 +136,11 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
     const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
     const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
     if (a.rows_fast) {
-      // channels-last: stage[r][k], 16-byte copies, a warp covers one 512-byte row per instruction
-      for (int r = warp; r < nrows; r += kLoadWarps) {
+      // channels-last: stage[r][k], 16-byte copies, a warp covers 512 contiguous bytes (1 or 2 rows) per instruction
+      for (int r = warp * kRowsPerInstr + sub_row; r < nrows; r += kLoadWarps * kRowsPerInstr) {
         const int q = w0 + r, b = b0 + q / W, w = q % W;
-        const float* src = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD + lane * 4;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pt::smem_u32(&s.stage[r * kD + lane * 4])), "l"(src) : "memory");
+        const float* src = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD + sub_col;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pt::smem_u32(&s.stage[r * kD + sub_col])), "l"(src) : "memory");
       }
     } else {
       // channel-first: stage[k][r], 4-byte copies, lanes = consecutive rows (w contiguous in memory)
@@ -135,30 +156,28 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   if (warp < kLoadWarps && part < a.n_tiles) prefetch(part);
-  // ---- prologue: stage the codebook once (warps 0-7: 16 code rows each, all loads in flight before any is used)
+  // ---- prologue: stage the codebook chunk once (warps 0-7: 16 code rows each, all loads in flight before any is used)
   if (warp < 8) {
-    constexpr int kPerWarp = kK / 8;
+    constexpr int kPerWarp = kK / 8 / kRowsPerInstr;
     float4 cv[kPerWarp];
 #pragma unroll
-    for (int i = 0; i < kPerWarp; ++i)
-      cv[i] = __ldg(reinterpret_cast<const float4*>(cb + (size_t)(warp + i * 8) * kD) + lane);
+    for (int i = 0; i < kPerWarp; ++i) {
+      const int j = (warp + i * 8) * kRowsPerInstr + sub_row;
+      cv[i] = (j < n_codes) ? __ldg(reinterpret_cast<const float4*>(cb + (size_t)j * kD + sub_col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     float sq[kPerWarp];
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i)
-      sq[i] = fmaf(cv[i].w, cv[i].w, fmaf(cv[i].z, cv[i].z, fmaf(cv[i].y, cv[i].y, cv[i].x * cv[i].x)));
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-      for (int i = 0; i < kPerWarp; ++i) sq[i] += __shfl_xor_sync(0xffffffffu, sq[i], o);
-    }
+      sq[i] = row_sum<kRowLanes>(fmaf(cv[i].w, cv[i].w, fmaf(cv[i].z, cv[i].z, fmaf(cv[i].y, cv[i].y, cv[i].x * cv[i].x))));
     float wmax = 0.f;
 #pragma unroll
     for (int i = 0; i < kPerWarp; ++i) {
-      const int j = warp + i * 8;
+      const int j = (warp + i * 8) * kRowsPerInstr + sub_row;
       wmax = fmaxf(wmax, sq[i]);
-      if (lane == 0) s.sc2[j] = sq[i];
-      split_store4(s.b_ops[0], s.b_ops[1], j, lane * 4, cv[i]);
+      if (sub_col == 0) s.sc2[j] = (j < n_codes) ? sq[i] : INFINITY;      // padding codes can never win
+      split_store4(s.b_ops[0], s.b_ops[1], j, sub_col, cv[i]);
     }
+    wmax = fmaxf(wmax, __shfl_xor_sync(0xffffffffu, wmax, 16));           // kRowLanes = 16: two rows per instruction
     if (lane == 0) s.cmax_w[warp] = sqrtf(wmax);
   }
   pt::fence_async_smem();
@@ -185,25 +204,25 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       float* sx2 = s.sx2[it & 3];        // 4-deep: a slot is rewritten only after the scan of that tile has retired
       if (a.rows_fast) {
 #pragma unroll 4
-        for (int r = warp; r < kTileRows; r += kLoadWarps) {
+        for (int r = warp * kRowsPerInstr + sub_row; r < kTileRows; r += kLoadWarps * kRowsPerInstr) {
           float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (r < nrows) x = *reinterpret_cast<const float4*>(&s.stage[r * kD + lane * 4]);
-          const float sq = warp_sum(fmaf(x.w, x.w, fmaf(x.z, x.z, fmaf(x.y, x.y, x.x * x.x))));
-          if (lane == 0) sx2[r] = sq;
-          split_store4(hi, lo, r, lane * 4, x);
+          if (r < nrows) x = *reinterpret_cast<const float4*>(&s.stage[r * kD + sub_col]);
+          const float sq = row_sum<kRowLanes>(fmaf(x.w, x.w, fmaf(x.z, x.z, fmaf(x.y, x.y, x.x * x.x))));
+          if (sub_col == 0) sx2[r] = sq;
+          split_store4(hi, lo, r, sub_col, x);
         }
       } else {
         const int r = tid;
         const bool live = r < nrows;
         float sq = 0.f;
 #pragma unroll 4
-        for (int chunk = 0; chunk < 16; ++chunk) {
+        for (int c8 = 0; c8 < kD / 8; ++c8) {
           float v[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = live ? s.stage[(chunk * 8 + i) * kTileRows + r] : 0.f;
+          for (int i = 0; i < 8; ++i) v[i] = live ? s.stage[(c8 * 8 + i) * kTileRows + r] : 0.f;
 #pragma unroll
           for (int i = 0; i < 8; ++i) sq = fmaf(v[i], v[i], sq);
-          split_store(hi, lo, (chunk >> 3) * kAtomBytes + pt::sw128_offset(r, chunk & 7), v);
+          split_store(hi, lo, (c8 >> 3) * kAtomBytes + pt::sw128_offset(r, c8 & 7), v);
         }
         sx2[r] = sq;
       }
@@ -273,8 +292,9 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
           const float sb = fmaf(-2.f, __uint_as_float(v[i + 1]), s.sc2[j + 1]);
           if constexpr (kDump) {
             if (r < nrows) {
-              a.score_dump[((row0 + r) * a.G + g) * kK + j] = sa;
-              a.score_dump[((row0 + r) * a.G + g) * kK + j + 1] = sb;
+              float* dump = a.score_dump + ((row0 + r) * a.G + g) * a.K + code0;
+              if (j < n_codes) dump[j] = sa;
+              if (j + 1 < n_codes) dump[j + 1] = sb;
             }
           }
           ma2 = fminf(ma2, fmaxf(sa, ma1));          // second-min update, then min (strict < keeps the first index)
@@ -289,7 +309,8 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       if (mb1 < ma1 || (mb1 == ma1 && ib < ia)) { best = mb1; bi = ib; second = fminf(ma1, mb2); }
       else { best = ma1; bi = ia; second = fminf(mb1, ma2); }
       const float band = 2.f * kBand * sqrtf(s.sx2[it & 3][r]) * cmax + 4e-7f * fabsf(best);
-      const bool amb = (r < nrows) && (second - best <= band);
+      // a chunk of a larger codebook re-scores EVERY row: the chunk winners are merged by their fp32 distances
+      const bool amb = (r < nrows) && (multi || second - best <= band);
       const unsigned amb_mask = __ballot_sync(0xffffffffu, amb);
       unsigned cand[4] = {0u, 0u, 0u, 0u};
       if (amb_mask) {                              // warp-uniform: second pass collects every code inside the band
@@ -323,10 +344,13 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
         const long long row = row0 + rr;
         const int q = w0 + rr, b = b0 + q / W, w = q % W;
         const float* px = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
-        float x[4];
+        float x[kD / 32];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) x[i] = __ldg(px + (size_t)(lane + 32 * i) * a.zs_c);
-        const float sx2 = warp_sum(fmaf(x[3], x[3], fmaf(x[2], x[2], fmaf(x[1], x[1], x[0] * x[0]))));
+        for (int i = 0; i < kD / 32; ++i) x[i] = __ldg(px + (size_t)(lane + 32 * i) * a.zs_c);
+        float xs = 0.f;
+#pragma unroll
+        for (int i = 0; i < kD / 32; ++i) xs = fmaf(x[i], x[i], xs);
+        const float sx2 = warp_sum(xs);
         float rbest = INFINITY, rsecond = INFINITY;
         int rbi = 0;
 #pragma unroll
@@ -338,7 +362,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
             const float* pc = cb + (size_t)j * kD;
             float dot = 0.f;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) dot = fmaf(x[i], __ldg(pc + lane + 32 * i), dot);
+            for (int i = 0; i < kD / 32; ++i) dot = fmaf(x[i], __ldg(pc + lane + 32 * i), dot);
             dot = warp_sum(dot);
             const float d = (sx2 + s.sc2[j]) - 2.f * dot;
             if (d < rbest) { rsecond = rbest; rbest = d; rbi = j; }      // ascending j: first minimum wins ties
@@ -346,9 +370,15 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
           }
         }
         if (lane == 0) {
-          a.idx_out[row * a.G + g] = rbi;
-          if (a.gap_out) a.gap_out[row * a.G + g] = rsecond - rbest;
-          if (a.n_rescored) atomicAdd(a.n_rescored, 1);
+          if (multi) {
+            const unsigned long long word = (static_cast<unsigned long long>(ordered_bits(rbest)) << 32) |
+                                            static_cast<unsigned>(code0 + rbi);
+            atomicMin(reinterpret_cast<unsigned long long*>(a.idx_out + row * a.G + g), word);
+          } else {
+            a.idx_out[row * a.G + g] = rbi;
+            if (a.gap_out) a.gap_out[row * a.G + g] = rsecond - rbest;
+          }
+          if (a.n_rescored && !multi) atomicAdd(a.n_rescored, 1);
         }
       }
     }
@@ -363,18 +393,19 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
 // out element (b, w, g*128 + d) at out + b*os_b + w*os_w + (g*128+d)*os_c ; fp32 or bf16
 template <typename OutT, typename IdxT>
 __global__ void pq_gather_kernel(const IdxT* __restrict__ idx, const float* __restrict__ cb, OutT* __restrict__ out,
-                                 long long os_b, long long os_w, long long os_c, int B, int W, int G, int* bad) {
-  const long long n = (long long)B * W * G * (kD / 4);
+                                 long long os_b, long long os_w, long long os_c, int B, int W, int G, int K, int D, int* bad) {
+  const int d4 = D / 4;
+  const long long n = (long long)B * W * G * d4;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const int q = (int)(i % (kD / 4));
-    const long long e = i / (kD / 4);          // (row, g)
+    const int q = (int)(i % d4);
+    const long long e = i / d4;                // (row, g)
     const int g = (int)(e % G);
     const long long row = e / G;
     const long long b = row / W, w = row % W;
     long long j = (long long)idx[e];
-    if (j < 0 || j >= kK) { if (bad) atomicAdd(bad, 1); j = 0; }
-    const float4 v = __ldg(reinterpret_cast<const float4*>(cb + ((size_t)g * kK + j) * kD) + q);
-    OutT* p = out + b * os_b + w * os_w + (long long)(g * kD + q * 4) * os_c;
+    if (j < 0 || j >= K) { if (bad && q == 0) atomicAdd(bad, 1); j = 0; }
+    const float4 v = __ldg(reinterpret_cast<const float4*>(cb + ((size_t)g * K + j) * D) + q);
+    OutT* p = out + b * os_b + w * os_w + (long long)(g * D + q * 4) * os_c;
     const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
@@ -450,25 +481,47 @@ extern "C" int pt_pq_gather_conv1x1(const void* idx, int idx_is_i64, const float
   return 0;
 }
 
+namespace {
+template <int kD>
+int launch_search(const PqArgs& a, unsigned grid, bool dump, cudaStream_t st) {
+  const size_t smem = sizeof(PqSmem<kD>) + 1024;
+  if (dump) {
+    PT_SMEM_OPT_IN((pq_search_kernel<kD, true>), smem);
+    pq_search_kernel<kD, true><<<grid, kThreads, smem, st>>>(a);
+  } else {
+    PT_SMEM_OPT_IN((pq_search_kernel<kD, false>), smem);
+    pq_search_kernel<kD, false><<<grid, kThreads, smem, st>>>(a);
+  }
+  PT_CUDA(cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
 extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long long zs_w, int B, int W, int G,
                             int K, int D, const float* codebooks, long long* idx_out, float* gap_out,
                             float* score_dump, int* n_rescored, void* stream) {
-  if (K != kK || D != kD) return pt::fail("pt_pq_search: only K = D = 128 is built (got K=%d D=%d)", K, D);
+  if (D != 64 && D != 128) return pt::fail("pt_pq_search: sub-vector width D must be 64 or 128 (got %d)", D);
+  if (K < 16 || (K & 15) || K > 65536) return pt::fail("pt_pq_search: K must be a multiple of 16 in [16, 65536] (got %d)", K);
   if (G < 1 || G > 65535) return pt::fail("pt_pq_search: bad group count %d", G);
   if (B < 0 || W < 0) return pt::fail("pt_pq_search: negative shape");
   if ((long long)B * W == 0) return 0;
   if (!z || !codebooks || !idx_out) return pt::fail("pt_pq_search: null pointer");
   if (reinterpret_cast<uintptr_t>(codebooks) & 15) return pt::fail("pt_pq_search: codebooks must be 16-byte aligned");
+  const int n_chunks = (K + kK - 1) / kK;
+  if (n_chunks > 1 && gap_out)
+    return pt::fail("pt_pq_search: gap_out is only available for K <= %d (got K=%d)", kK, K);
   const int sms = pt::sm_count();
+  cudaStream_t st = (cudaStream_t)stream;
   PqArgs a;
-  a.z = z; a.zs_b = zs_b; a.zs_w = zs_w; a.zs_c = zs_c; a.B = B; a.W = W; a.G = G;
+  a.z = z; a.zs_b = zs_b; a.zs_w = zs_w; a.zs_c = zs_c; a.B = B; a.W = W; a.G = G; a.K = K;
   a.codebooks = codebooks; a.idx_out = idx_out; a.gap_out = gap_out; a.score_dump = score_dump;
-  a.n_rescored = n_rescored;
+  a.n_rescored = n_rescored; a.n_chunks = n_chunks;
   a.rows_fast = (zs_c == 1 && !(reinterpret_cast<uintptr_t>(z) & 15) && !(zs_b & 3) && !(zs_w & 3)) ? 1 : 0;
   const long long rows = (long long)B * W;
-  // persistent CTAs: `per_group` CTAs per sub-codebook, each walking k tiles; tile height chosen so that the tiles
-  // divide evenly (a tile costs ~ its rows, so 2 x 77 rows beats 128 + 25)
-  int per_group = sms / G;
+  const int vgroups = G * n_chunks;                  // (sub-codebook, chunk of 128 codes) pairs; a CTA serves one
+  // persistent CTAs: `per_group` CTAs per (sub-codebook, chunk), each walking k tiles; tile height chosen so that the
+  // tiles divide evenly (a tile costs ~ its rows, so 2 x 77 rows beats 128 + 25)
+  int per_group = sms / vgroups;
   if (per_group < 1) per_group = 1;
   const long long full_tiles = (rows + kTileRows - 1) / kTileRows;
   if (full_tiles < per_group) per_group = (int)full_tiles;
@@ -479,32 +532,37 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   a.rows_per_tile = (int)R;
   a.n_tiles = (int)((rows + R - 1) / R);
   a.ctas_per_group = per_group;
-  const size_t smem = sizeof(PqSmem) + 1024;
-  PT_SMEM_OPT_IN(pq_search_kernel<false>, smem);
-  PT_SMEM_OPT_IN(pq_search_kernel<true>, smem);
-  const unsigned grid = (unsigned)(per_group * G);
-  if (score_dump) pq_search_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
-  else pq_search_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
-  PT_CUDA(cudaGetLastError());
+  const unsigned grid = (unsigned)(per_group * vgroups);
+  if (n_chunks > 1)      // packed (distance, index) words are folded into idx_out with atomicMin: start from all ones
+    PT_CUDA(cudaMemsetAsync(idx_out, 0xff, sizeof(long long) * (size_t)rows * G, st));
+  const int rc = (D == 128) ? launch_search<128>(a, grid, score_dump != nullptr, st)
+                            : launch_search<64>(a, grid, score_dump != nullptr, st);
+  if (rc) return rc;
+  if (n_chunks > 1) {
+    const long long n = rows * G;
+    pq_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(idx_out, n);
+    PT_CUDA(cudaGetLastError());
+  }
   return 0;
 }
 
 extern "C" int pt_pq_gather(const void* idx, int idx_is_i64, const float* codebooks, void* out, int out_is_bf16,
                             long long os_b, long long os_c, long long os_w, int B, int W, int G, int K, int D,
                             int* bad_count, void* stream) {
-  if (K != kK || D != kD) return pt::fail("pt_pq_gather: only K = D = 128 is built (got K=%d D=%d)", K, D);
-  const long long n = (long long)B * W * G * (kD / 4);
+  if (K < 1 || D < 4 || (D & 3)) return pt::fail("pt_pq_gather: need K >= 1 and D a positive multiple of 4 (got K=%d D=%d)", K, D);
+  const long long n = (long long)B * W * G * (D / 4);
   if (n == 0) return 0;
   if (!idx || !codebooks || !out) return pt::fail("pt_pq_gather: null pointer");
+  if (reinterpret_cast<uintptr_t>(codebooks) & 15) return pt::fail("pt_pq_gather: codebooks must be 16-byte aligned");
   const int threads = 256;
   const int blocks = (int)min((long long)148 * 8, (n + threads - 1) / threads);
   cudaStream_t st = (cudaStream_t)stream;
   if (idx_is_i64) {
-    if (out_is_bf16) pq_gather_kernel<__nv_bfloat16, long long><<<blocks, threads, 0, st>>>((const long long*)idx, codebooks, (__nv_bfloat16*)out, os_b, os_w, os_c, B, W, G, bad_count);
-    else pq_gather_kernel<float, long long><<<blocks, threads, 0, st>>>((const long long*)idx, codebooks, (float*)out, os_b, os_w, os_c, B, W, G, bad_count);
+    if (out_is_bf16) pq_gather_kernel<__nv_bfloat16, long long><<<blocks, threads, 0, st>>>((const long long*)idx, codebooks, (__nv_bfloat16*)out, os_b, os_w, os_c, B, W, G, K, D, bad_count);
+    else pq_gather_kernel<float, long long><<<blocks, threads, 0, st>>>((const long long*)idx, codebooks, (float*)out, os_b, os_w, os_c, B, W, G, K, D, bad_count);
   } else {
-    if (out_is_bf16) pq_gather_kernel<__nv_bfloat16, int><<<blocks, threads, 0, st>>>((const int*)idx, codebooks, (__nv_bfloat16*)out, os_b, os_w, os_c, B, W, G, bad_count);
-    else pq_gather_kernel<float, int><<<blocks, threads, 0, st>>>((const int*)idx, codebooks, (float*)out, os_b, os_w, os_c, B, W, G, bad_count);
+    if (out_is_bf16) pq_gather_kernel<__nv_bfloat16, int><<<blocks, threads, 0, st>>>((const int*)idx, codebooks, (__nv_bfloat16*)out, os_b, os_w, os_c, B, W, G, K, D, bad_count);
+    else pq_gather_kernel<float, int><<<blocks, threads, 0, st>>>((const int*)idx, codebooks, (float*)out, os_b, os_w, os_c, B, W, G, K, D, bad_count);
   }
   PT_CUDA(cudaGetLastError());
   return 0;

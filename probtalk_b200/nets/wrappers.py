@@ -109,6 +109,43 @@ class PQLayer(M.ProductQuantizationParams):
         return QuantizationOutput(q, idx)
 
 
+class VectorQuantizerEMA(torch.nn.Module):
+    """Inference surface of the single-codebook quantizer of the TalkSHOW-style VQ-VAEs (vqvae_modules.py:279-377, built
+    with embedding_dim = 64, num_embeddings = config.Model.code_num by nets/smplx_body_vq.py:48-53): the ``embeddings``
+    buffer with the reference's name / shape, ``get_code_indices`` (:350-358), ``quantize`` (:360-362) and the eval
+    ``forward`` (indices -> quantized, [B, D, T] in and out).  The search is pt_pq_search with G = 1."""
+
+    def __init__(self, embedding_dim, num_embeddings, commitment_cost=0.25, decay=0.99, epsilon=1e-5):
+        super().__init__()
+        self.embedding_dim, self.num_embeddings = embedding_dim, num_embeddings
+        self.commitment_cost, self.decay, self.epsilon = commitment_cost, decay, epsilon
+        self.register_buffer("embeddings", torch.zeros(num_embeddings, embedding_dim))
+        self.register_buffer("ema_dw", torch.zeros(num_embeddings, embedding_dim))
+        self.register_buffer("ema_cluster_size", torch.zeros(num_embeddings))
+
+    def get_code_indices(self, flat_x):
+        """flat_x [N, D] (CUDA fp32) -> indices [N] int64."""
+        cb = self.embeddings.to(flat_x.device, torch.float32).unsqueeze(0).contiguous()
+        z = flat_x.to(torch.float32).contiguous().t().unsqueeze(0)            # [1, D, N] view, channels-last strides
+        return ops.pq_search(z, cb).reshape(-1)
+
+    def quantize(self, encoding_indices):
+        idx = encoding_indices.reshape(1, -1, 1)
+        q, bad = ops.pq_gather(idx.to(self.embeddings.device), self.embeddings.float().unsqueeze(0).contiguous(),
+                               channels_last=True)
+        if int(bad) != 0:
+            raise IndexError("code index out of range in quantize")
+        return q.reshape(*encoding_indices.shape, self.embedding_dim)
+
+    def forward(self, x):
+        """Eval path of vqvae_modules.py:305-343: x [B, D, T] -> (quantized [B, D, T], loss = 0)."""
+        B, D, T = x.shape
+        flat = x.permute(0, 2, 1).reshape(-1, D)
+        idx = self.get_code_indices(flat)
+        q = self.quantize(idx).view(B, T, D).permute(0, 2, 1).contiguous()
+        return q, torch.zeros((), device=x.device)
+
+
 class VQVAE(M.VQVAE_SC):
     """VQVAE_SC with the reference's call surface (vqvae_1d_sc.py:277-324) on top of the CUDA plans."""
 

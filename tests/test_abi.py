@@ -68,9 +68,15 @@ def test_argument_validation_without_gpu(lib):
     """Entry points reject bad arguments before touching the device."""
     lib.pt_pq_search.restype = ctypes.c_int
     lib.pt_last_error.restype = ctypes.c_char_p
-    rc = lib.pt_pq_search(None, ctypes.c_longlong(0), ctypes.c_longlong(0), ctypes.c_longlong(0), 1, 1, 4, 64, 64, None,
+    rc = lib.pt_pq_search(None, ctypes.c_longlong(0), ctypes.c_longlong(0), ctypes.c_longlong(0), 1, 1, 4, 64, 96, None,
                           None, None, None, None, None)
-    assert rc != 0 and b"K = D = 128" in lib.pt_last_error()
+    assert rc != 0 and b"D must be 64 or 128" in lib.pt_last_error()
+    rc = lib.pt_pq_search(None, ctypes.c_longlong(0), ctypes.c_longlong(0), ctypes.c_longlong(0), 1, 1, 4, 100, 64, None,
+                          None, None, None, None, None)
+    assert rc != 0 and b"multiple of 16" in lib.pt_last_error()
+    rc = lib.pt_pq_search(None, ctypes.c_longlong(0), ctypes.c_longlong(0), ctypes.c_longlong(0), 1, 1, 1, 2048, 64, None,
+                          None, None, None, None, None)
+    assert rc != 0 and b"null pointer" in lib.pt_last_error()          # G = 1, K = 2048, D = 64 is a valid shape
     lib.pt_attention.restype = ctypes.c_int
     rc = lib.pt_attention(ctypes.c_void_p(16), ctypes.c_longlong(8), ctypes.c_void_p(16), ctypes.c_longlong(8),
                           ctypes.c_void_p(16), ctypes.c_longlong(8), ctypes.c_void_p(16), ctypes.c_longlong(8), 1, 8, 32,

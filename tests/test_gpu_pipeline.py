@@ -356,13 +356,14 @@ def oracle_sets(states):
     sets = []
     for seed in (302, 303):
         u, gum = noise(8, aud.shape[0], 88, seed)
-        outs, codes = [], []
+        outs, codes, preds = [], [], []
         for i in range(0, aud.shape[0], 64):                      # oracle in slices of 64 (memory)
             sl = slice(i, i + 64)
             p, c = O.predictor_infer_on_batch(aud[sl], gt[sl], mask[sl], labels[sl], pst, vq, u[:, sl], gum[:, sl])
             outs.append(O.refiner_infer_on_batch(aud[sl], gt[sl], mask[sl], labels[sl], p, rst["HFTransformer"]))
+            preds.append(p)
             codes.append(c)
-        sets.append((torch.cat(outs), torch.cat(codes)))
+        sets.append((torch.cat(outs), torch.cat(codes), torch.cat(preds)))
     return sets
 
 
@@ -383,9 +384,11 @@ def test_fgd_lvd_diversity_unchanged(states, oracle_sets, precision):
     u, gum = noise(8, B, 88, 302)
     gpu, codes = pipe.window(aud.cuda(), gt.cuda(), mask.cuda(), labels.int().cuda(), noise=(u.cuda(), gum.cuda()))
     gpu, codes = gpu.clone(), codes.cpu().long()
-    (ora, ora_codes), (ora2, _) = oracle_sets
+    gpu_pred = pipe.predictor(B, 180).out.clone()                      # the predictor's poses of the same run (stage 1)
+    (ora, ora_codes, ora_pred), (ora2, _, ora2_pred) = oracle_sets
     agree = (codes == ora_codes.long()).float().mean().item()
     real = S.synthetic_poses(B, 180, 304)                              # a fixed "real" set for FGD(generated, real)
+    realc = real.cuda()
 
     def feats(p):
         c = _chunks90(p.cuda().float())
@@ -395,32 +398,36 @@ def test_fgd_lvd_diversity_unchanged(states, oracle_sets, precision):
         (ma, sa), (mb, sb) = EV.feature_stats(fa), EV.feature_stats(fb)
         return EV.frechet_distance(ma.cpu().numpy(), sa.cpu().numpy(), mb.cpu().numpy(), sb.cpu().numpy())
 
-    f_gpu, f_ora, f_ora2, f_real = feats(gpu), feats(ora), feats(ora2), feats(real)
-    assert f_gpu.shape == (2 * B, 128)
-    fd_same, fd_yard = fgd(f_gpu, f_ora), fgd(f_ora2, f_ora)          # same noise: CUDA vs oracle; yardstick: oracle vs oracle
-    g_gpu, g_ora, g_ora2 = fgd(f_gpu, f_real), fgd(f_ora, f_real), fgd(f_ora2, f_real)
-
     def per_clip(fn, p):
         p = p.cuda().float()
-        return sum(fn(p[c * N_SAMPLES:(c + 1) * N_SAMPLES]) for c in range(N_CLIPS)) / N_CLIPS
+        return sum(fn(p[c * N_SAMPLES:(c + 1) * N_SAMPLES], c) for c in range(N_CLIPS)) / N_CLIPS
 
-    div = lambda p: per_clip(lambda x: EV.diversity(x.transpose(1, 2))[0], p)                     # [16, 180, 376]
     kp = lambda x: x[:, :276].transpose(1, 2).reshape(x.shape[0], 180, 46, 6)                     # 46 joints x 6-D
-    realc = real.cuda()
-    lvd = lambda p: sum(EV.lvd(kp(realc[c * N_SAMPLES:c * N_SAMPLES + 1])[0], kp(p.cuda().float()[c * N_SAMPLES:(c + 1) * N_SAMPLES]))[0]
-                        for c in range(N_CLIPS)) / N_CLIPS
-    d_gpu, d_ora, d_ora2 = div(gpu), div(ora), div(ora2)
-    l_gpu, l_ora, l_ora2 = lvd(gpu), lvd(ora), lvd(ora2)
-    print("[%s] code agreement %.4f | FGD(cuda, oracle same noise) %.4f vs yardstick FGD(oracle B, oracle A) %.4f | "
-          "FGD vs real: cuda %.3f oracle %.3f oracle-B %.3f | diversity %.5f / %.5f / %.5f | LVD %.4f / %.4f / %.4f"
-          % (precision, agree, fd_same, fd_yard, g_gpu, g_ora, g_ora2, d_gpu, d_ora, d_ora2, l_gpu, l_ora, l_ora2))
-    # unchanged = closer to the oracle than a second oracle run with other noise is
-    assert fd_same <= fd_yard + 1e-6, (fd_same, fd_yard)
-    assert abs(g_gpu - g_ora) <= max(1.5 * abs(g_ora2 - g_ora), 0.01 * g_ora), (g_gpu, g_ora, g_ora2)
-    assert abs(d_gpu - d_ora) <= max(1.5 * abs(d_ora2 - d_ora), 0.01 * d_ora), (d_gpu, d_ora, d_ora2)
-    assert abs(l_gpu - l_ora) <= max(1.5 * abs(l_ora2 - l_ora), 0.01 * l_ora), (l_gpu, l_ora, l_ora2)
-    if precision == "bf16x3":
-        # fp32-grade logits: the sampler takes the oracle's decisions, so the metrics coincide, not just "stay close"
-        assert agree >= 0.995
-        assert fd_same <= 0.02 * fd_yard and abs(g_gpu - g_ora) <= 1e-3 * g_ora
-        assert abs(d_gpu - d_ora) <= 1e-3 * d_ora and abs(l_gpu - l_ora) <= 1e-3 * l_ora
+    div = lambda p: per_clip(lambda x, c: EV.diversity(x.transpose(1, 2))[0], p)                  # [16, 180, 376] per clip
+    lvd = lambda p: per_clip(lambda x, c: EV.lvd(kp(realc[c * N_SAMPLES:c * N_SAMPLES + 1])[0], kp(x))[0], p)
+    f_real = feats(real)
+    # eps = the stated mean-abs pose tolerance of this arithmetic at each stage (the bf16 bounds of this file; SURVEY's
+    # 1e-4 for bf16x3): independent errors of that size can move a mean pairwise L1 distance by at most 2 eps
+    for stage, a, o, o2, eps in (("predictor", gpu_pred, ora_pred, ora2_pred, BOUND["decode"][1] if precision == "bf16" else 1e-4),
+                                 ("refined", gpu, ora, ora2, BOUND["refiner"][1] if precision == "bf16" else 1e-4)):
+        f_a, f_o, f_o2 = feats(a), feats(o), feats(o2)
+        assert f_a.shape == (2 * B, 128)
+        fd_same, fd_yard = fgd(f_a, f_o), fgd(f_o2, f_o)      # same noise: CUDA vs oracle; yardstick: oracle vs oracle
+        g_a, g_o, g_o2 = fgd(f_a, f_real), fgd(f_o, f_real), fgd(f_o2, f_real)
+        d_a, d_o, d_o2 = div(a), div(o), div(o2)
+        l_a, l_o, l_o2 = lvd(a), lvd(o), lvd(o2)
+        print("[%s %s] code agreement %.4f | FGD(cuda, oracle) %.2e, yardstick FGD(oracle B, oracle A) %.2e | FGD vs real: cuda "
+              "%.4f oracle %.4f oracle-B %.4f | diversity %.5f / %.5f / %.5f | LVD %.4f / %.4f / %.4f"
+              % (precision, stage, agree, fd_same, fd_yard, g_a, g_o, g_o2, d_a, d_o, d_o2, l_a, l_o, l_o2))
+        # "unchanged": as close to the oracle as a second oracle run with other sampler noise is, or inside what the stated
+        # pose tolerance of the arithmetic can move the metric (the synthetic checkpoints give samples that differ less
+        # between noise draws than bf16 rounding moves them, so the second clause is the binding one for bf16)
+        assert fd_same <= max(1.5 * fd_yard, 1e-4 * g_o), (stage, fd_same, fd_yard, g_o)
+        assert abs(g_a - g_o) <= max(1.5 * abs(g_o2 - g_o), 2e-3 * g_o), (stage, g_a, g_o, g_o2)
+        assert abs(d_a - d_o) <= max(1.5 * abs(d_o2 - d_o), 2 * eps), (stage, d_a, d_o, d_o2)
+        assert abs(l_a - l_o) <= max(1.5 * abs(l_o2 - l_o), 2e-3 * l_o), (stage, l_a, l_o, l_o2)
+        if precision == "bf16x3":
+            # fp32-grade logits: the sampler takes the oracle's decisions, so the metrics coincide, not just "stay close"
+            assert agree >= 0.995
+            assert fd_same <= 1e-6 * g_o and abs(g_a - g_o) <= 1e-4 * g_o
+            assert abs(d_a - d_o) <= 1e-4 + 1e-3 * d_o and abs(l_a - l_o) <= 1e-4 * l_o

@@ -102,7 +102,9 @@ def test_empty_and_errors():
     idx = ops.pq_search(torch.zeros(0, 512, 22, device="cuda"), cb)
     assert idx.shape == (0, 22, 4)
     with pytest.raises(PtError):
-        ops.pq_search(torch.zeros(2, 256, 4, device="cuda"), torch.zeros(4, 64, 64, device="cuda"))
+        ops.pq_search(torch.zeros(2, 384, 4, device="cuda"), torch.zeros(4, 64, 96, device="cuda"))      # D = 96 is not built
+    with pytest.raises(PtError):
+        ops.pq_search(torch.zeros(2, 256, 4, device="cuda"), torch.zeros(4, 40, 64, device="cuda"))      # K % 16 != 0
     with pytest.raises(PtError):
         ops.pq_search(torch.zeros(2, 512, 4), _codebooks("xavier", 1))      # CPU tensors: no fallback
 
@@ -141,7 +143,7 @@ def test_channels_last_input_and_gather_roundtrip():
     idx_bad = idx.clone()
     idx_bad[0, 0, 0] = 999
     _, bad = ops.pq_gather(idx_bad, cb.cuda())
-    assert int(bad) == 32                                         # one bad (row, group) = 32 float4 lanes
+    assert int(bad) == 1                                          # one bad (row, group) entry
 
 
 def test_full_size_properties():
@@ -160,3 +162,56 @@ def test_full_size_properties():
         dj = ((flat - cb[:, j][None]) ** 2).sum(-1)
         assert bool((dq <= dj + 1e-3).all())
     assert torch.equal(ops.pq_search(q, cb), idx)
+
+
+@pytest.mark.parametrize("G,K,D,B,W", [(1, 2048, 64, 64, 37), (1, 512, 64, 7, 5), (1, 64, 64, 33, 22), (2, 16, 128, 9, 4),
+                                       (4, 144, 128, 16, 22), (3, 128, 64, 256, 22), (1, 2048, 128, 5, 9)])
+@pytest.mark.parametrize("scale", [1.0, 0.1])
+def test_generalized_shapes_vs_oracle(G, K, D, B, W, scale):
+    """J1: VectorQuantizerEMA.get_code_indices (vqvae_modules.py:350-358; smplx_body_vq.py:48-53: one codebook,
+    embedding_dim = 64, num_embeddings = code_num = 2048) and other (G, K, D) -- the same formula, the same near-tie bar.
+    K > 128 goes through the chunked search (fp32 chunk winners merged by packed atomicMin)."""
+    from probtalk_b200 import ops
+    g = torch.Generator().manual_seed(G * 1000 + K + D)
+    z = torch.randn(B, G * D, W, generator=g) * scale
+    cb = torch.randn(G, K, D, generator=g) * (1.0 if K < 1024 else 0.3)
+    for zz in (z.cuda(), z.permute(0, 2, 1).contiguous().cuda().permute(0, 2, 1)):      # channel-first and channels-last
+        idx = ops.pq_search(zz, cb.cuda())
+        torch.cuda.synchronize()
+        assert int(idx.min()) >= 0 and int(idx.max()) < K
+        _check(z, cb, idx)
+    # duplicated codes: the FIRST of two identical codes must win, across chunk boundaries too
+    cb2 = cb.clone()
+    if K >= 32:
+        cb2[:, K - 1] = cb2[:, 3]
+        x = cb2[:, 3].reshape(1, G * D, 1).repeat(2, 1, 3)
+        idx = ops.pq_search(x.cuda(), cb2.cuda()).cpu()
+        assert bool((idx == 3).all())
+    # gather with the same codebooks
+    q, bad = ops.pq_gather(ops.pq_search(z.cuda(), cb.cuda()), cb.cuda())
+    ref = O.pq_gather(O.pq_search(z, [cb[i] for i in range(G)]), [cb[i] for i in range(G)]).transpose(1, 2)
+    same = ops.pq_search(z.cuda(), cb.cuda()).cpu() == O.pq_search(z, [cb[i] for i in range(G)])
+    assert int(bad) == 0 and q.shape == ref.shape
+    if bool(same.all()):
+        assert torch.equal(q.cpu(), ref)
+
+
+def test_vector_quantizer_ema_facade():
+    """nets.VectorQuantizerEMA: same buffer names as the reference layer, indices equal to its formula."""
+    import probtalk_b200.nets as nets
+    vq = nets.VectorQuantizerEMA(64, 2048).cuda()
+    assert set(vq.state_dict()) == {"embeddings", "ema_dw", "ema_cluster_size"}
+    g = torch.Generator().manual_seed(5)
+    vq.embeddings.copy_(torch.randn(2048, 64, generator=g) * 0.3)
+    x = torch.randn(3, 64, 50, generator=g)
+    flat = x.permute(0, 2, 1).reshape(-1, 64)
+    idx = vq.get_code_indices(flat.cuda()).cpu()
+    emb = vq.embeddings.cpu()
+    dist = (flat ** 2).sum(1, keepdim=True) + (emb ** 2).sum(1) - 2.0 * flat @ emb.t()       # vqvae_modules.py:352-356
+    ref = dist.argmin(1)
+    d64 = (flat.double() ** 2).sum(1, keepdim=True) + (emb.double() ** 2).sum(1) - 2.0 * flat.double() @ emb.double().t()
+    top2 = d64.topk(2, dim=1, largest=False).values
+    bad = idx != ref
+    assert bool(((top2[:, 1] - top2[:, 0])[bad] < 1e-4).all()) and bad.float().mean() < 0.01
+    q, _ = vq(x.cuda())
+    assert q.shape == x.shape and torch.equal(q.cpu().permute(0, 2, 1).reshape(-1, 64), emb[idx])
