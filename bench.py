@@ -222,10 +222,21 @@ def run_ours(args):
     if world > 1:
         # NCCL's INIT log (communicator size, transport, NVLS) goes to STDERR, so that it can be inspected while stdout
         # stays the single JSON line of rank 0
-        os.environ.setdefault("NCCL_DEBUG", os.environ.get("PT_BENCH_NCCL_DEBUG", "INFO"))
+        # NCCL's INIT log (communicator size, transport, NVLS) must be visible, but stdout is ONE JSON line: the log goes
+        # to a per-process file that every rank copies to stderr before it exits, and while NCCL initialises (it prints its
+        # version banner straight to stdout) file descriptor 1 points at stderr
+        os.environ["NCCL_DEBUG"] = os.environ.get("PT_BENCH_NCCL_DEBUG", "INFO")
         os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        nccl_log = os.path.join(tempfile.gettempdir(), "pt_bench_nccl_%d.log" % os.getpid())
+        os.environ["NCCL_DEBUG_FILE"] = nccl_log
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
+        dist.barrier()                                     # communicator set-up happens here, banner included
+        torch.cuda.synchronize()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     _lib.lib()
     B = args.batch
     vq, pst, rst = S.make_vq_state(0), S.make_predictor_state(1), S.make_refiner_state(5)
@@ -342,6 +353,12 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+        try:
+            with open(nccl_log) as f:
+                sys.stderr.write(f.read())
+            os.unlink(nccl_log)
+        except OSError:
+            pass
 
 
 def _time_steps(fn, steps, warm=2):

@@ -55,6 +55,23 @@ int pt_pq_gather(const void* idx, int idx_is_i64, const float* codebooks, void* 
                  long long os_b, long long os_c, long long os_w, int B, int W, int G, int K, int D, int* bad_count,
                  void* stream);
 
+/* Training-side update of the product quantizer: the EMA codebook update and dead-code reset that
+ * ProductQuantization.forward performs in training mode, nets/spg/vqvae_modules.py:495-534 (share_code = False) with
+ * ExponentialMovingAverage.forward :271-276, plus the commitment term F.mse_loss(x, quantized) of :537.
+ *   z, zs_*      the encoder output of this batch, addressed like pt_pq_search;  idx [B, W, G] int64 its codes
+ *   codebooks [G, K, D], ema_dw [G, K, D] (`ema_dw.{g}.hidden`), ema_cluster_size [G, K] (`ema_cluster_size.{g}.hidden`):
+ *                fp32 state, updated in place;  step = the reference's EMA counter AFTER its increment (1, 2, ...)
+ *   mse_out      fp64 [1] or NULL: mean |x - codebook_before[idx]|^2 (multiply by commitment_cost for the loss)
+ *   dead_out     int32 [G] or NULL: codes re-seeded from the batch this step (normalised EMA cluster size < 1)
+ *   workspace    device memory, 8-byte aligned, pt_pq_ema_workspace_bytes(G, K, D) bytes (contents clobbered)
+ * Needs B*W >= K (the reference re-seeds from the first K rows of the batch; with fewer rows it adds torch.randn noise,
+ * which is refused here).  Deterministic: fixed summation order, no floating-point atomics. */
+long long pt_pq_ema_workspace_bytes(int G, int K, int D);
+int pt_pq_ema_update(const float* z, long long zs_b, long long zs_c, long long zs_w, int B, int W, int G, int K, int D,
+                     const long long* idx, float* codebooks, float* ema_dw, float* ema_cluster_size, double decay,
+                     double epsilon, int step, double* mse_out, int* dead_out, void* workspace, long long workspace_bytes,
+                     void* stream);
+
 /* Codebook gather fused into the decoder's first convolution.  Replaces quantize_all (nets/spg/vqvae_modules.py:557-564)
  * followed by DecoderSC.aft_vq_conv, the 1x1 Conv1d(G*D -> N) at nets/inpainting/vqvae_1d_sc.py:259-261:
  *   out[b, w, n] = bias[n] + sum_g table[g][idx[b, w, g]][n],   table[g] = C_g . W[:, g*D:(g+1)*D]^T  (fp32 [G, K, N],

@@ -458,3 +458,39 @@ def refiner_infer_on_batch(aud, gt_poses, mask, ids, pred_poses, ref_sd):
     blank = gt_poses * mask + pred_poses * (1 - mask)
     out = rtransformer(blank, aud, mask, ids, ref_sd)
     return gt_poses * mask + out * (1 - mask)
+
+
+# --------------------------------------------------------------------------------------
+# training-side quantizer update
+# --------------------------------------------------------------------------------------
+
+
+def pq_ema_update(z, idx, codebooks, ema_dw, ema_cs, decay, eps, step):
+    """EMA codebook update + dead-code reset of ProductQuantization.forward (training, share_code = False),
+    nets/spg/vqvae_modules.py:495-534 with ExponentialMovingAverage.forward :271-276.
+    z [B, G*D, W], idx [B, W, G]; codebooks / ema_dw: lists of [K, D], ema_cs: list of [K] (the `.hidden` buffers), all
+    updated in place; step = the EMA counter after its increment.  Returns mse(x, quantized) (:537)."""
+    B, C, W = z.shape
+    G = len(codebooks)
+    K, D = codebooks[0].shape
+    flat_x = z.permute(0, 2, 1).reshape(-1, G, D)
+    quantized = torch.cat([F.embedding(idx[..., g].reshape(-1), codebooks[g]) for g in range(G)], dim=-1)
+    mse = F.mse_loss(flat_x.reshape(-1, G * D), quantized)
+    for g in range(G):
+        x = flat_x[:, g]
+        encodings = F.one_hot(idx[..., g].reshape(-1), K).float()
+        ema_cs[g].sub_((ema_cs[g] - torch.sum(encodings, dim=0)) * (1 - decay))
+        cs = ema_cs[g] / (1 - decay ** step)
+        n = torch.sum(cs)
+        cs = (cs + eps) / (n + K * eps) * n
+        dw = torch.matmul(encodings.t(), x)
+        ema_dw[g].sub_((ema_dw[g] - dw) * (1 - decay))
+        w = (ema_dw[g] / (1 - decay ** step)) / cs.reshape(-1, 1)
+        assert x.shape[0] >= K, "the reference's _tile adds torch.randn noise when the batch has fewer rows than codes"
+        code_rand = x[:K]
+        usage = (cs.view(K, 1) >= 1.0).float()
+        ema_dw[g].copy_(usage * ema_dw[g] + (1 - usage) * code_rand)
+        ema_cs[g].mul_(usage.view(-1))
+        ema_cs[g].add_(torch.ones_like(ema_cs[g]) * (1 - usage).view(-1))
+        codebooks[g].copy_(usage * w + (1 - usage) * code_rand)
+    return mse

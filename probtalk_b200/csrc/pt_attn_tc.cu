@@ -120,6 +120,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   pt::tc_fence_before();
   __syncthreads();
   pt::tc_fence_after();
+  pt::pdl_launch_dependents();      // set-up done: the next kernel may start its own; q / k / v / out are dependent memory
+  pt::pdl_wait();
   const uint32_t tmem = tmem_slot;
   const uint32_t tmem_s = tmem, tmem_o = tmem + (uint32_t)a.o_col;
   const uint32_t p_bytes = (uint32_t)p_atoms * kAtomBytes;
@@ -503,7 +505,7 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
 #define PT_ATTN_LAUNCH(K)                                                                                              \
   do {                                                                                                                 \
     PT_SMEM_OPT_IN(attention_tc_kernel<K>, smem);                                                                      \
-    attention_tc_kernel<K><<<grid, kThreadsTc, smem, st>>>(tq, tk, tv, a);                                             \
+    PT_CUDA(pt::launch_pdl(attention_tc_kernel<K>, dim3(grid), dim3(kThreadsTc), smem, st, 1, tq, tk, tv, a));         \
   } while (0)
   if (nch == 1) PT_ATTN_LAUNCH(1);
   else if (nch == 2) PT_ATTN_LAUNCH(2);

@@ -30,6 +30,16 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may begin while its predecessor in the stream
+// is still running (once every CTA of the predecessor has executed pdl_launch_dependents or exited).  pdl_wait blocks
+// the calling thread until the predecessor grid has completed and its memory is visible: EVERY thread calls it before it
+// touches global memory that the predecessor may write or still read; what comes before it (barrier init, TMEM
+// allocation, descriptor prefetch, staging of weights) overlaps the predecessor's tail.  Both are no-ops for a kernel
+// launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -68,6 +68,8 @@ __global__ void pack_rows_kernel(PackArgs a) {
 constexpr int kPackMaxT = 384;
 template <int kIters>                                  // time steps per lane: T <= 32 * kIters
 __global__ void __launch_bounds__(256, 5) pack_rows_slab_kernel(PackArgs a) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   extern __shared__ float slab[];                      // [32][T + 1]
   __shared__ float mask_s[kPackMaxT];
   const int b = blockIdx.y, c0 = blockIdx.x * 32;
@@ -149,6 +151,8 @@ __global__ void __launch_bounds__(256, 5) pack_rows_slab_kernel(PackArgs a) {
 //                mode 1 -> two channels one_hot(mask.long(), 2) (RTransformer.py:218): ch0 = (mask==0), ch1 = (mask==1)
 __global__ void pack_mask_kernel(const float* __restrict__ mask, __nv_bfloat16* __restrict__ dst, int B, int T, int Tp,
                                  int H, int Cp, int c_off, int mode) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * T) return;
   const int b = i / T, t = i % T;
@@ -186,6 +190,8 @@ __global__ void blend_kernel(const float* __restrict__ known, const float* __res
 __global__ void __launch_bounds__(256) blend_rows_kernel(const float* __restrict__ known, const float* __restrict__ mask,
                                                          const float* __restrict__ pred, float* __restrict__ out,
                                                          unsigned rows, unsigned C, int T, int Tpred, int mask_pow) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   const unsigned row = blockIdx.x * 8u + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -219,6 +225,8 @@ __global__ void __launch_bounds__(256) blend_rows_kernel(const float* __restrict
 __global__ void blend_vec4_kernel(const float4* __restrict__ known, const float* __restrict__ mask,
                                   const float4* __restrict__ pred, float4* __restrict__ out, unsigned n4, unsigned T4,
                                   unsigned C, int mask_pow) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
     const unsigned bc = i / T4, t4 = i - bc * T4, b = bc / C;
     const float4 m = __ldg(reinterpret_cast<const float4*>(mask) + (size_t)b * T4 + t4);
@@ -356,6 +364,8 @@ __global__ void embed_tokens_kernel(const int* __restrict__ tokens, const float*
                                     const double* __restrict__ pe64, float* __restrict__ out32,
                                     __nv_bfloat16* __restrict__ out16, __nv_bfloat16* __restrict__ out16_lo, int M, int N,
                                     int n_emb, int* bad) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -391,6 +401,8 @@ __global__ void __launch_bounds__(128) maskgit_step_kernel(const float* __restri
                                                             const float* __restrict__ u, const float* __restrict__ gumbel,
                                                             int* __restrict__ next, int N, int mask_id, int base_len,
                                                             float temperature) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   __shared__ float conf[kMaxTokens];
   __shared__ int samp[kMaxTokens];
   __shared__ float pbuf[4][kCodes];
@@ -463,8 +475,8 @@ extern "C" int pt_pack_rows(const float* src, const float* mask, const float* pr
   PackArgs a{src, mask, pred, (__nv_bfloat16*)dst_bf16, B, C, T, Tp, H, Cp, c_off, mode, pred_T, (__nv_bfloat16*)dst_lo};
   if (T <= kPackMaxT && B <= 65535) {
     const size_t smem = (size_t)32 * (T + 1) * sizeof(float);   // <= 48 KB
-    if (T <= 192) pack_rows_slab_kernel<6><<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
-    else pack_rows_slab_kernel<12><<<dim3((C + 31) / 32, B), 256, smem, (cudaStream_t)stream>>>(a);
+    if (T <= 192) PT_CUDA(pt::launch_pdl(pack_rows_slab_kernel<6>, dim3((C + 31) / 32, B), dim3(256), smem, (cudaStream_t)stream, 1, a));
+    else PT_CUDA(pt::launch_pdl(pack_rows_slab_kernel<12>, dim3((C + 31) / 32, B), dim3(256), smem, (cudaStream_t)stream, 1, a));
   } else {
     dim3 grid((T + 31) / 32, (C + 31) / 32, B), block(32, 8);
     pack_rows_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(a);
@@ -478,8 +490,8 @@ extern "C" int pt_pack_mask(const float* mask, void* dst_bf16, int B, int T, int
   if (B <= 0 || T <= 0) return 0;
   if (!mask || !dst_bf16) return pt::fail("pt_pack_mask: null pointer");
   const int n = B * T;
-  pack_mask_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(mask, (__nv_bfloat16*)dst_bf16, B, T, Tp, H, Cp,
-                                                                     c_off, onehot ? 1 : 0);
+  PT_CUDA(pt::launch_pdl(pack_mask_kernel, dim3((n + 255) / 256), dim3(256), 0, (cudaStream_t)stream, 1, mask,
+                         (__nv_bfloat16*)dst_bf16, B, T, Tp, H, Cp, c_off, onehot ? 1 : 0));
   PT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -495,11 +507,12 @@ extern "C" int pt_interp_blend(const float* known, const float* mask, const floa
   if (pred_T == T && T % 4 == 0 && aligned && n / 4 < (1LL << 31)) {
     const unsigned n4 = (unsigned)(n / 4);
     const unsigned blocks = (n4 + 255) / 256;          // one float4 per thread: no loop-carried latency
-    blend_vec4_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const float4*)known, mask, (const float4*)pred,
-                                                                 (float4*)out, n4, (unsigned)(T / 4), (unsigned)C, mask_pow);
+    PT_CUDA(pt::launch_pdl(blend_vec4_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, 1, (const float4*)known, mask,
+                           (const float4*)pred, (float4*)out, n4, (unsigned)(T / 4), (unsigned)C, mask_pow));
   } else if ((long long)B * C < (1LL << 31)) {
     const unsigned rows = (unsigned)B * (unsigned)C;
-    blend_rows_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(known, mask, pred, out, rows, (unsigned)C, T, pred_T, mask_pow);
+    PT_CUDA(pt::launch_pdl(blend_rows_kernel, dim3((rows + 7) / 8), dim3(256), 0, (cudaStream_t)stream, 1, known, mask, pred, out,
+                           rows, (unsigned)C, T, pred_T, mask_pow));
   } else {
     const int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
     blend_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(known, mask, pred, out, B, C, T, pred_T, mask_pow);
@@ -543,8 +556,8 @@ extern "C" int pt_embed_tokens512(const int* tokens, const float* emb, int n_emb
   if (M <= 0) return 0;
   if (!tokens || !emb || !pe64 || (!out_f32 && !out_bf16)) return pt::fail("pt_embed_tokens512: null pointer");
   if (N <= 0) return pt::fail("pt_embed_tokens512: N must be positive");
-  embed_tokens_kernel<<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>(tokens, emb, pe64, out_f32, (__nv_bfloat16*)out_bf16,
-                                                                    (__nv_bfloat16*)out_lo, M, N, n_emb, bad_count);
+  PT_CUDA(pt::launch_pdl(embed_tokens_kernel, dim3((M + 7) / 8), dim3(256), 0, (cudaStream_t)stream, 1, tokens, emb, pe64, out_f32,
+                         (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M, N, n_emb, bad_count));
   PT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -556,8 +569,8 @@ extern "C" int pt_maskgit_step(const float* logits, const int* cur_ids, const fl
   if (!logits || !cur_ids || !u || !gumbel || !next_ids) return pt::fail("pt_maskgit_step: null pointer");
   if (n_codes != kCodes) return pt::fail("pt_maskgit_step: only %d codes are built (got %d)", kCodes, n_codes);
   if (N > kMaxTokens) return pt::fail("pt_maskgit_step: at most %d tokens per sample (got %d)", kMaxTokens, N);
-  maskgit_step_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(logits, cur_ids, u, gumbel, next_ids, N, mask_id,
-                                                          base_mask_len, temperature);
+  PT_CUDA(pt::launch_pdl(maskgit_step_kernel, dim3(B), dim3(128), 0, (cudaStream_t)stream, 1, logits, cur_ids, u, gumbel, next_ids,
+                         N, mask_id, base_mask_len, temperature));
   PT_CUDA(cudaGetLastError());
   return 0;
 }

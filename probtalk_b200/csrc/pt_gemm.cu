@@ -209,6 +209,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   pt::tc_fence_after();
   if constexpr (kClusterSize > 1) cluster_sync_all();  // the peers' barriers exist before anyone arrives on them
   const uint32_t tmem_base = *tmem_slot;
+  // set-up done: the next kernel of the stream may start ITS set-up; everything below reads / writes dependent memory
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   // Register re-balancing for the row-norm variant (setmaxnreg acts on a warpgroup of 4 warps): the producer / MMA /
   // idle warps keep 40 registers, the two epilogue warpgroups grow to 232 so that a thread can hold its row's 128 fp32
   // accumulators across the LayerNorm.  128 * 40 + 256 * 232 = 64512 = 384 * 168, what the kernel is launched with.
@@ -906,21 +909,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, 
   const int tiles = m_super * ka.N_tiles;
   int clusters = sms / CL;
   if (tiles < clusters) clusters = tiles;
-  if constexpr (CL == 1) {
-    gemm_kernel<BN, false, 1><<<clusters, kThreads, Cfg<BN>::kSmem, st>>>(ta, tb, to, tr, ka);
-    PT_CUDA(cudaGetLastError());
-  } else {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(CL * clusters);
-    cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = Cfg<BN>::kSmem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, false, CL>, ta, tb, to, tr, ka));
-  }
+  PT_CUDA(pt::launch_pdl(gemm_kernel<BN, false, CL>, dim3(CL * clusters), dim3(kThreads), Cfg<BN>::kSmem, st, CL, ta, tb, to, tr, ka));
   return 0;
 }
 
@@ -931,16 +920,7 @@ int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap&
   const int tiles = ((ka.m_tiles + 1) / 2) * ka.N_tiles;
   int pairs = sms / 2;
   if (tiles < pairs) pairs = tiles;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * pairs);
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = Cf::kSmem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, false, 1, true>, ta, tb, to, tr, ka));
+  PT_CUDA(pt::launch_pdl(gemm_kernel<256, false, 1, true>, dim3(2 * pairs), dim3(kThreads), Cf::kSmem, st, 2, ta, tb, to, tr, ka));
   return 0;
 }
 
@@ -949,16 +929,7 @@ int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorM
   PT_SMEM_OPT_IN((gemm_kernel<256, true, 1>), Cfg<256>::kSmem);
   int clusters = sms / 2;
   if (ka.m_tiles < clusters) clusters = ka.m_tiles;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * clusters);
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = Cfg<256>::kSmem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
-  PT_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<256, true, 1>, ta, tb, to, tr, ka));
+  PT_CUDA(pt::launch_pdl(gemm_kernel<256, true, 1>, dim3(2 * clusters), dim3(kThreads), Cfg<256>::kSmem, st, 2, ta, tb, to, tr, ka));
   return 0;
 }
 

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <atomic>
 
 namespace pt {
@@ -45,6 +46,39 @@ struct PerDevice {
     return v[dev & 63];
   }
 };
+
+// PT_PDL=0 turns programmatic dependent launch off (A/B measurements); read once
+inline bool pdl_enabled() {
+  static const bool on = !(getenv("PT_PDL") && atoi(getenv("PT_PDL")) == 0);
+  return on;
+}
+
+// Launch `kernel` so that it may overlap the tail of its predecessor in the stream (programmatic dependent launch;
+// the kernel calls pt::pdl_wait() before it touches dependent memory), optionally as clusters of `cluster` CTAs.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (cluster > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = (unsigned)cluster; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 }  // namespace pt
 

@@ -21,6 +21,7 @@
 // HBM traffic: z once (fp32), codebook from L2, int64 indices out.  No scratch memory.
 #include "pt_common.cuh"
 #include "pt_host.h"
+#include <stdlib.h>
 
 namespace {
 
@@ -92,6 +93,7 @@ struct PqArgs {
   int rows_per_tile, n_tiles, ctas_per_group;
   int n_chunks;                 // ceil(K / 128): a CTA is bound to ONE (sub-codebook, chunk of 128 codes)
   int rows_fast;                // 1: channels-last rows, 16-byte aligned -> float4 row loader
+  long long* trace;             // developer hook (PT_PQ_TRACE): clock64 stamps of CTA 0's roles, [3 roles][32]
 };
 
 // Codebooks with more than 128 codes (VectorQuantizerEMA, code_num = 2048): every chunk's CTAs find the chunk's fp32
@@ -120,6 +122,11 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   const float* cb = a.codebooks + ((size_t)g * a.K + code0) * kD;
   const int W = a.W;
   const int sub_row = lane / kRowLanes, sub_col = (lane % kRowLanes) * 4;
+  int n_stamp = 0;
+  auto stamp = [&](int role) {       // role 0 = loader warp 0, 1 = MMA issuer, 2 = scan warp 0
+    if (a.trace && blockIdx.x == 0 && lane == 0 && n_stamp < 32) a.trace[role * 32 + n_stamp++] = clock64();
+  };
+  if (warp == 0) stamp(0);
 
   if (warp == kLoadWarps) {                       // the MMA warp also owns TMEM
     pt::tmem_alloc(&s.tmem_base, 256);
@@ -185,6 +192,9 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
   __syncthreads();
   pt::tc_fence_after();
   const uint32_t tmem = s.tmem_base;
+  if (warp == 0) stamp(0);                                   // codebook staged, set-up done
+  if (warp == kLoadWarps) stamp(1);
+  if (warp == kLoadWarps + 1) stamp(2);
 
   if (warp < kLoadWarps) {
     // ------------------------------------------------------------ loaders
@@ -198,7 +208,9 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
       asm volatile("cp.async.wait_group 0;" ::: "memory");
       asm volatile("bar.sync 1, 128;" ::: "memory");        // every loader thread's copies have landed
+      if (warp == 0) stamp(0);                               // rows landed
       pt::mbar_wait(&s.a_empty, ph ^ 1);                    // the MMAs of the previous tile have read the operands
+      if (warp == 0) stamp(0);                               // operand buffer free
       uint8_t* hi = s.a_ops[0];
       uint8_t* lo = s.a_ops[1];
       float* sx2 = s.sx2[it & 3];        // 4-deep: a slot is rewritten only after the scan of that tile has retired
@@ -229,6 +241,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       pt::fence_async_smem();                                // generic-proxy smem writes -> tensor-core proxy
       asm volatile("bar.sync 1, 128;" ::: "memory");        // everyone is done reading `stage`
       if (lane == 0) pt::mbar_arrive(&s.a_full);
+      if (warp == 0) stamp(0);                               // converted
       const int nt = t + a.ctas_per_group;
       if (nt < a.n_tiles) prefetch(nt);
     }
@@ -244,6 +257,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
         pt::mbar_wait(&s.a_full, (uint32_t)it & 1u);
         pt::mbar_wait(&s.t_empty[buf], ph ^ 1);
         pt::tc_fence_after();
+        stamp(1);                                            // operands + accumulator ready
         const uint32_t a_hi = pt::smem_u32(s.a_ops[0]), a_lo = pt::smem_u32(s.a_ops[1]);
         const uint32_t pa[3] = {a_hi, a_hi, a_lo}, pb[3] = {b_hi, b_lo, b_hi};
         uint32_t acc = 0;
@@ -258,6 +272,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
         }
         pt::umma_commit(&s.t_full[buf]);
         pt::umma_commit(&s.a_empty);
+        stamp(1);                                            // issued
       }
     }
   } else {
@@ -276,6 +291,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
       pt::mbar_wait(&s.t_full[buf], ph);
       pt::tc_fence_after();
+      if (warp == kLoadWarps + 1) stamp(2);                  // scores ready
       const uint32_t t_row = tmem + buf * 128 + (static_cast<uint32_t>(qd * 32) << 16);
       // two independent (min, argmin, second-min) trackers (even / odd columns) for instruction-level parallelism
       float ma1 = INFINITY, ma2 = INFINITY, mb1 = INFINITY, mb2 = INFINITY;
@@ -330,6 +346,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       pt::tc_fence_before();
       __syncwarp();
       if (lane == 0) pt::mbar_arrive(&s.t_empty[buf]);       // the accumulator may be overwritten from here on
+      if (warp == kLoadWarps + 1) stamp(2);                  // scanned
       if (!amb && r < nrows) {
         a.idx_out[(row0 + r) * a.G + g] = bi;
         if (a.gap_out) a.gap_out[(row0 + r) * a.G + g] = second - best;
@@ -381,6 +398,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
           if (a.n_rescored && !multi) atomicAdd(a.n_rescored, 1);
         }
       }
+      if (warp == kLoadWarps + 1) stamp(2);                  // re-scored, written
     }
   }
   pt::tc_fence_before();
@@ -429,6 +447,8 @@ __global__ void __launch_bounds__(256) pq_gather_conv_kernel(const IdxT* __restr
                                                               __nv_bfloat16* __restrict__ out_lo, long long oss,
                                                               long long ors, long long rows, int W, int G, int K, int N,
                                                               int* bad) {
+  pt::pdl_launch_dependents();
+  pt::pdl_wait();
   const int per_row = N >> 3;
   const long long total = rows * per_row;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -472,11 +492,11 @@ extern "C" int pt_pq_gather_conv1x1(const void* idx, int idx_is_i64, const float
   const int blocks = (int)min((long long)pt::sm_count() * 8, (total + 255) / 256);
   cudaStream_t st = (cudaStream_t)stream;
   if (idx_is_i64)
-    pq_gather_conv_kernel<long long><<<blocks, 256, 0, st>>>((const long long*)idx, table, bias, (__nv_bfloat16*)out_bf16,
-                                                             (__nv_bfloat16*)out_lo, oss, ors, rows, W, G, K, N, bad_count);
+    PT_CUDA(pt::launch_pdl(pq_gather_conv_kernel<long long>, dim3(blocks), dim3(256), 0, st, 1, (const long long*)idx, table, bias,
+                           (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, oss, ors, rows, W, G, K, N, bad_count));
   else
-    pq_gather_conv_kernel<int><<<blocks, 256, 0, st>>>((const int*)idx, table, bias, (__nv_bfloat16*)out_bf16,
-                                                       (__nv_bfloat16*)out_lo, oss, ors, rows, W, G, K, N, bad_count);
+    PT_CUDA(pt::launch_pdl(pq_gather_conv_kernel<int>, dim3(blocks), dim3(256), 0, st, 1, (const int*)idx, table, bias,
+                           (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, oss, ors, rows, W, G, K, N, bad_count));
   PT_CUDA(cudaGetLastError());
   return 0;
 }
@@ -516,6 +536,10 @@ extern "C" int pt_pq_search(const float* z, long long zs_b, long long zs_c, long
   a.z = z; a.zs_b = zs_b; a.zs_w = zs_w; a.zs_c = zs_c; a.B = B; a.W = W; a.G = G; a.K = K;
   a.codebooks = codebooks; a.idx_out = idx_out; a.gap_out = gap_out; a.score_dump = score_dump;
   a.n_rescored = n_rescored; a.n_chunks = n_chunks;
+  {
+    const char* e = getenv("PT_PQ_TRACE");                 // developer hook: device address of 96 int64 (hex or decimal)
+    a.trace = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
+  }
   a.rows_fast = (zs_c == 1 && !(reinterpret_cast<uintptr_t>(z) & 15) && !(zs_b & 3) && !(zs_w & 3)) ? 1 : 0;
   const long long rows = (long long)B * W;
   const int vgroups = G * n_chunks;                  // (sub-codebook, chunk of 128 codes) pairs; a CTA serves one

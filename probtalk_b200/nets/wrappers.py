@@ -100,6 +100,29 @@ class PQLayer(M.ProductQuantizationParams):
             raise IndexError("code index out of range in quantize_all")
         return q.reshape(*lead, -1)
 
+    def train_forward(self, z, commitment_cost=0.25, decay=0.99, epsilon=1e-5):
+        """ProductQuantization.forward in TRAINING mode (vqvae_modules.py:470-545, share_code = False): nearest-code search,
+        EMA codebook update + dead-code reset on this module's own buffers (pt_pq_ema_update), commitment loss.  Returns
+        QuantizationOutput(quantized [B, G*D, W] -- the straight-through VALUE, no autograd graph --, loss)."""
+        dev = self.__dict__["_owner"]()._device
+        z = z.to(dev, torch.float32)
+        G = self.num_chunks
+        cb = torch.stack([getattr(self, "embeddings_%d" % g).to(dev, torch.float32) for g in range(G)]).contiguous()
+        dw = torch.stack([self.ema_dw[g].hidden.to(dev, torch.float32) for g in range(G)]).contiguous()
+        cs = torch.stack([self.ema_cluster_size[g].hidden.to(dev, torch.float32) for g in range(G)]).contiguous()
+        idx = ops.pq_search(z, cb)
+        q, _ = ops.pq_gather(idx, cb)                                   # quantized with the codebooks BEFORE the update
+        self.__dict__["_ema_step"] = self.__dict__.get("_ema_step", 0) + 1
+        mse, _ = ops.pq_ema_update(z, idx, cb, dw, cs, decay, epsilon, self.__dict__["_ema_step"])
+        with torch.no_grad():
+            for g in range(G):
+                getattr(self, "embeddings_%d" % g).copy_(cb[g])
+                self.ema_dw[g].hidden.copy_(dw[g])
+                self.ema_cluster_size[g].hidden.copy_(cs[g])
+        owner = self.__dict__["_owner"]()
+        owner._weights, owner._plans = None, E.PlanCache()              # prepared weights / plans hold the old codebooks
+        return QuantizationOutput(q, commitment_cost * mse.to(torch.float32)[0])
+
     def forward(self, z, r=0.0, **kw):
         """ProductQuantization.forward in eval mode (vqvae_modules.py:470-492)."""
         W = self._weights()

@@ -177,3 +177,25 @@ def attention_f32(q, k, v, B, Nq, Nk, heads=8, head_dim=64, scale=None, split=Tr
                                       out.data_ptr(), _ptr(lo), heads * head_dim, B, heads, head_dim, Nq, Nk, scale,
                                       _stream()), "pt_attention_f32")
     return out, lo
+
+
+def pq_ema_update(z, idx, codebooks, ema_dw, ema_cluster_size, decay, epsilon, step):
+    """EMA codebook update + dead-code reset of ProductQuantization's training forward (pt_pq_ema_update;
+    vqvae_modules.py:495-534).  z [B, G*D, W] fp32 (any strides), idx [B, W, G] int64; codebooks [G, K, D], ema_dw [G, K, D]
+    and ema_cluster_size [G, K] are updated IN PLACE.  Returns (mse fp64 [1], re-seeded codes per group int32 [G])."""
+    _need_cuda(z, idx, codebooks, ema_dw, ema_cluster_size)
+    G, K, D = codebooks.shape
+    B, Cc, W = z.shape
+    assert Cc == G * D and idx.shape == (B, W, G) and idx.dtype == torch.int64 and idx.is_contiguous()
+    for t in (codebooks, ema_dw, ema_cluster_size):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    L = _lib.lib()
+    nbytes = L.pt_pq_ema_workspace_bytes(G, K, D)
+    ws = torch.empty((nbytes + 7) // 8, dtype=torch.float64, device=z.device)
+    mse = torch.zeros(1, dtype=torch.float64, device=z.device)
+    dead = torch.zeros(G, dtype=torch.int32, device=z.device)
+    sb, sc, sw = z.stride()
+    check(L.pt_pq_ema_update(z.data_ptr(), sb, sc, sw, B, W, G, K, D, idx.data_ptr(), codebooks.data_ptr(), ema_dw.data_ptr(),
+                             ema_cluster_size.data_ptr(), float(decay), float(epsilon), int(step), mse.data_ptr(),
+                             dead.data_ptr(), ws.data_ptr(), nbytes, _stream()), "pt_pq_ema_update")
+    return mse, dead

@@ -78,3 +78,28 @@ def test_graph_replay_equals_eager(pipe):
         outs.append((poses.clone(), codes.clone(), ref.clone()))
     for a, b in zip(outs[0], outs[1]):
         assert torch.equal(a, b)
+
+
+def test_second_device_in_one_process():
+    """Per-device kernel set-up (dynamic shared-memory opt-ins, SM count): a process that runs plans on cuda:0 and then on
+    cuda:1 (the reference wraps its models in nn.DataParallel) must get the same results on both."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from probtalk_b200 import driver as D
+    B, T = 2, 180
+    aud, gt = S.synthetic_audio(B, T, 95), S.synthetic_poses(B, T, 96)
+    mask = torch.zeros(B, 1, T)
+    mask[:, :, :30] = 1
+    labels = torch.tensor([1, 2], dtype=torch.int32)
+    g = torch.Generator().manual_seed(3)
+    u = torch.rand(8, B, 88, generator=g)
+    gum = -torch.log(-torch.log(torch.rand(8, B, 88, generator=g).clamp_(1e-10, 1 - 1e-7)))
+    outs = []
+    for dev in ("cuda:0", "cuda:1"):
+        pipe = D.HolisticPipeline(S.make_vq_state(0), S.make_predictor_state(1), S.make_refiner_state(5), dev)
+        out, codes = pipe.window(aud.to(dev), gt.to(dev), mask.to(dev), labels.to(dev), noise=(u.to(dev), gum.to(dev)))
+        x = S.synthetic_poses(1, 300, 7).to(dev)
+        from probtalk_b200 import engine as E
+        enc_codes = E.EncoderPlan(pipe.VW, 1, 300).run(x).cpu()
+        outs.append((out.cpu(), codes.cpu(), enc_codes))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
