@@ -141,9 +141,6 @@ __device__ __forceinline__ void welford_merge(float& n, float& mean, float& m2, 
 // kRowNorm: launched as clusters of two CTAs; CTA `rank` owns columns [rank*256, rank*256+256) of the same 128
 // rows, and the two exchange per-row (sum, sum of squares) partials through distributed shared memory so that the epilogue can
 // apply a LayerNorm over the full 512-wide row (StylizationBlock_V3 / norm1-3 of the reference) in place.
-// kCL > 1 (plain variant only): clusters of kCL CTAs along M work on kCL consecutive 128-row tiles of the SAME
-// column tile; every CTA loads 1/kCL of the weight box and multicasts it to the whole cluster, so weight traffic
-// from L2 drops by kCL (these GEMMs have K = 512..2048 and are L2-bandwidth bound with private weight loads).
 // k2: pairs of CTAs (cta_group::2) compute a 256-row x BN tile together: the leader's MMA thread issues
 // M = 256 instructions that read 128 A rows and BN/2 weight rows from EACH CTA's smem, so a CTA stages (and the tensor
 // core reads) half the weight bytes per FLOP; stages shrink to 32 KB and the ring deepens from 4 to 6.
@@ -172,7 +169,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __shared__ uint64_t stats_bar[2];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  static_assert(!(kRowNorm && kCL != 1), "row-norm clusters are along N");
+  static_assert(kCL == 1, "every CTA loads its own weight tiles (no clusters along M)");
   static_assert(!(k2 && (kRowNorm || kCL != 1)), "cta_group::2 is its own variant");
   constexpr int kClusterSize = (kRowNorm || k2) ? 2 : kCL;
   const uint32_t rank = (kClusterSize > 1) ? cluster_ctarank() : 0u;
@@ -185,7 +182,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   const int n_tiles_total = kRowNorm ? p.m_tiles : m_super * p.N_tiles;
   auto tile_m0 = [&](int tile) { return kRowNorm ? tile * BM : ((tile / p.N_tiles) * kRowBlocks + (int)rank) * BM; };
   auto tile_n0 = [&](int tile) { return kRowNorm ? (int)rank * BN : (tile % p.N_tiles) * BN; };
-  constexpr uint16_t kMcMask = (uint16_t)((1u << kCL) - 1u);
 
   if (warp == 0 && lane == 0) {
     pt::tma_prefetch_desc(&tmap_a);
@@ -299,14 +295,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           }
           pt::mbar_expect_tx(&full[stage], C::kStageBytes);
           pt::tma_load_2d(sa, tma, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
-          if constexpr (kCL == 1) {
-            pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0);
-          } else {
-            // this CTA's slice of the weight box (BN / kCL rows), delivered to every CTA of the cluster
-            constexpr int kSliceRows = BN / kCL;
-            pt::tma_load_2d_mc(sa + C::kABytes + rank * (kSliceRows * 128), &tmap_b, &full[stage], wcol,
-                               n0 + (int)rank * kSliceRows, kMcMask);
-          }
+          pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -339,8 +328,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             pt::umma_commit_2sm(&empty[stage], 3);                  // both CTAs' slots are free
             if (kk == p.K_iters - 1) pt::umma_commit_2sm(&tmem_full[acc], 3);   // both CTAs' accumulators are ready
           } else {
-            if constexpr (kCL == 1) pt::umma_commit(&empty[stage]);   // slot reusable once these MMAs have read it
-            else pt::umma_commit_mc(&empty[stage], kMcMask);          // ... in every CTA that multicasts into it
+            pt::umma_commit(&empty[stage]);                         // slot reusable once these MMAs have read it
             if (kk == p.K_iters - 1 && !(kRowNorm && p.res_mma)) pt::umma_commit(&tmem_full[acc]);
           }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -1002,14 +990,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     const char* e = getenv("PT_GEMM_BN");                 // developer override: force 128-column tiles
     if (e && !d->row_norm && atoi(e) == 128) BN = 128;
   }
-  // Weight multicast across clusters of CTAs along M (CL = 2 / 4) is implemented and tested, but measured no
-  // faster than private loads on B200 (CL = 2: +2 %, CL = 4: -40 %, profiles/r01_notes.md): these GEMMs are bound by
-  // the bytes in flight per SM, not by L2 bandwidth.  Default off.
-  int CL = 1;
-  {
-    const char* e = getenv("PT_GEMM_CLUSTER");            // developer override (1, 2 or 4)
-    if (e && !d->row_norm && BN == 256) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) CL = v; }
-  }
+  constexpr int CL = 1;
   // cta_group::2 pairs for the big plain GEMMs (PT_GEMM_2CTA=0 disables, for A/B measurements)
   bool two_cta = false;
   {
@@ -1019,7 +1000,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   }
   // split arithmetic: weight rows are [hi (taps*C) | lo (taps*C)]
   const long long wcols = (long long)(d->split ? 2 : 1) * d->taps * d->C;
-  if (make_tmap(&tb, d->w, d->N, wcols, wcols, two_cta ? 128 : BN / CL)) return 1;
+  if (make_tmap(&tb, d->w, d->N, wcols, wcols, two_cta ? 128 : BN)) return 1;
 
   GemmKernelArgs ka;
   ka.M = d->M; ka.N_tiles = d->N / BN; ka.c_iters = d->C / BK; ka.k_base = d->taps * ka.c_iters;
@@ -1064,7 +1045,5 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   if (d->row_norm) return launch_rownorm(ta, tb, to, tr, ka, sms, st);
   if (two_cta) return launch_2cta(ta, tb, to, tr, ka, sms, st);
   if (BN == 128) return launch<128, 1>(ta, tb, to, tr, ka, sms, st);
-  if (CL == 4) return launch<256, 4>(ta, tb, to, tr, ka, sms, st);
-  if (CL == 2) return launch<256, 2>(ta, tb, to, tr, ka, sms, st);
   return launch<256, 1>(ta, tb, to, tr, ka, sms, st);
 }
