@@ -6,10 +6,12 @@
 // Search = dense contraction:  score[r, j] = |c_j|^2 - 2 * x_r . c_j   (|x_r|^2 is constant per row and
 // cannot change the argmin).  Persistent, warp-specialised CTAs; a CTA is bound to ONE sub-codebook and
 // walks 128-row query tiles of it:
-//   prologue      8 warps stage the 128x128 codebook once as split-bf16 operands (c = c_hi + c_lo), K-major,
-//                 SWIZZLE_128B, and its squared norms;
-//   loader warps  (4) stream the next tile's raw fp32 rows into smem with cp.async while the previous tile is in
-//                 the tensor core / being scanned, then split them (x = x_hi + x_lo) into the bf16 operand tile;
+//   prologue      the raw fp32 codebook chunk lands in the (still idle) second query-operand buffer with cp.async -- every
+//                 thread's copies in flight at once --, then 8 warps split it into bf16 operands (c = c_hi + c_lo),
+//                 K-major, SWIZZLE_128B, and reduce its squared norms;
+//   loader warps  (8) read the next tile's fp32 rows straight from global memory (eight 512-byte rows in flight per
+//                 warp), split them (x = x_hi + x_lo) and write the bf16 operand tile of the OTHER operand buffer while
+//                 the previous tile is in the tensor core / being scanned;
 //   MMA warp      one thread issues 24 tcgen05.mma per tile (hi*hi + hi*lo + lo*hi) into one of two 128-column
 //                 TMEM accumulators; dropped terms are O(2^-16), so scores are within
 //                 E = 2.5e-4 * |x| * max|c| of exact (checked on hardware by tests/test_gpu_pq.py);
@@ -27,21 +29,21 @@ namespace {
 
 constexpr int kK = 128;          // codes per staged codebook chunk (UMMA N); larger codebooks are split into chunks
 constexpr int kTileRows = 128;   // UMMA M
-constexpr int kLoadWarps = 4, kScanWarps = 4;
-constexpr int kThreads = (kLoadWarps + 1 + kScanWarps) * 32;   // 288: loaders, MMA issuer, scanners
+constexpr int kLoadWarps = 8, kScanWarps = 4;
+constexpr int kThreads = (kLoadWarps + 1 + kScanWarps) * 32;   // 416: loaders, MMA issuer, scanners
+constexpr int kSxParts = 8;                                    // partial |x|^2 sums kept per row (summed by the scanner)
 constexpr uint32_t kAtomBytes = kTileRows * 128;    // 16 KB: one 64-column SWIZZLE_128B atom of a 128-row operand tile
 constexpr float kBand = 2.5e-4f;                    // rigorous bound is ~9.3e-5 * |x||c| on the dot, x2 for the score
 
 template <int kD>                  // sub-vector width: 128 (ProductQuantization, vq.json) or 64 (VectorQuantizerEMA)
 struct PqSmem {
   static constexpr uint32_t kOpBytes = kTileRows * kD * 2;   // one bf16 operand tile (kD / 64 swizzle atoms)
-  uint8_t a_ops[2][kOpBytes];      // query tile hi | lo (each 1024-B aligned)
-  float stage[kTileRows * kD];     // raw fp32 rows of the NEXT tile, filled asynchronously with cp.async
+  uint8_t a_ops[2][2][kOpBytes];   // query tile, double-buffered: [buffer][hi | lo] (each 1024-B aligned)
   uint8_t b_ops[2][kOpBytes];      // codebook chunk hi | lo
   float sc2[kK];                   // |c_j|^2 (fp32, deterministic order); +inf for the padding rows of a short chunk
-  float sx2[4][kTileRows];         // |x_r|^2, ring of 4 tiles (only used for the error band)
+  float sx2p[4][kSxParts][kTileRows];   // partial |x_r|^2, ring of 4 tiles (only used for the error band)
   float cmax_w[8];
-  uint64_t a_full, a_empty, t_full[2], t_empty[2];
+  uint64_t a_full[2], a_empty[2], t_full[2], t_empty[2];
   uint32_t tmem_base;
 };
 
@@ -133,56 +135,31 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
     pt::tmem_relinquish();
   }
   if (tid == 0) {
-    pt::mbar_init(&s.a_full, kLoadWarps); pt::mbar_init(&s.a_empty, 1);
+    for (int i = 0; i < 2; ++i) { pt::mbar_init(&s.a_full[i], kLoadWarps); pt::mbar_init(&s.a_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&s.t_full[i], 1); pt::mbar_init(&s.t_empty[i], kScanWarps); }
     pt::fence_mbar_init();
   }
-  // the first tile's rows start streaming before anything else happens
-  auto prefetch = [&](int t) {
-    const long long row0 = (long long)t * a.rows_per_tile;
-    const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
-    const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
-    if (a.rows_fast) {
-      // channels-last: stage[r][k], 16-byte copies, a warp covers 512 contiguous bytes (1 or 2 rows) per instruction
-      for (int r = warp * kRowsPerInstr + sub_row; r < nrows; r += kLoadWarps * kRowsPerInstr) {
-        const int q = w0 + r, b = b0 + q / W, w = q % W;
-        const float* src = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD + sub_col;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pt::smem_u32(&s.stage[r * kD + sub_col])), "l"(src) : "memory");
-      }
-    } else {
-      // channel-first: stage[k][r], 4-byte copies, lanes = consecutive rows (w contiguous in memory)
-      const int r = tid;
-      if (r < nrows) {
-        const int q = w0 + r, b = b0 + q / W, w = q % W;
-        const float* prow = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
-#pragma unroll 8
-        for (int k = 0; k < kD; ++k)
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(pt::smem_u32(&s.stage[k * kTileRows + r])), "l"(prow + (size_t)k * a.zs_c) : "memory");
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-  if (warp < kLoadWarps && part < a.n_tiles) prefetch(part);
-  // ---- prologue: stage the codebook chunk once (warps 0-7: 16 code rows each, all loads in flight before any is used)
+  // ---- prologue: the raw chunk (n_codes x kD fp32 <= 64 KB) goes global -> smem with cp.async, all copies of all threads in
+  // flight together (register-staged loads serialise under this kernel's register budget); the second query-operand
+  // buffer is idle until the loaders' second tile, which starts only after the __syncthreads below
+  float* craw = reinterpret_cast<float*>(&s.a_ops[1][0][0]);
+  for (int i = tid; i < n_codes * (kD / 4); i += kThreads)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pt::smem_u32(craw + (size_t)i * 4)), "l"(cb + (size_t)i * 4) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) stamp(0);                                   // raw codebook chunk in shared memory
   if (warp < 8) {
     constexpr int kPerWarp = kK / 8 / kRowsPerInstr;
-    float4 cv[kPerWarp];
-#pragma unroll
-    for (int i = 0; i < kPerWarp; ++i) {
-      const int j = (warp + i * 8) * kRowsPerInstr + sub_row;
-      cv[i] = (j < n_codes) ? __ldg(reinterpret_cast<const float4*>(cb + (size_t)j * kD + sub_col)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    float sq[kPerWarp];
-#pragma unroll
-    for (int i = 0; i < kPerWarp; ++i)
-      sq[i] = row_sum<kRowLanes>(fmaf(cv[i].w, cv[i].w, fmaf(cv[i].z, cv[i].z, fmaf(cv[i].y, cv[i].y, cv[i].x * cv[i].x))));
     float wmax = 0.f;
-#pragma unroll
+#pragma unroll 4
     for (int i = 0; i < kPerWarp; ++i) {
       const int j = (warp + i * 8) * kRowsPerInstr + sub_row;
-      wmax = fmaxf(wmax, sq[i]);
-      if (sub_col == 0) s.sc2[j] = (j < n_codes) ? sq[i] : INFINITY;      // padding codes can never win
-      split_store4(s.b_ops[0], s.b_ops[1], j, sub_col, cv[i]);
+      const float4 cv = (j < n_codes) ? *reinterpret_cast<const float4*>(craw + (size_t)j * kD + sub_col) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float sq = row_sum<kRowLanes>(fmaf(cv.w, cv.w, fmaf(cv.z, cv.z, fmaf(cv.y, cv.y, cv.x * cv.x))));
+      wmax = fmaxf(wmax, sq);
+      if (sub_col == 0) s.sc2[j] = (j < n_codes) ? sq : INFINITY;         // padding codes can never win
+      split_store4(s.b_ops[0], s.b_ops[1], j, sub_col, cv);
     }
     wmax = fmaxf(wmax, __shfl_xor_sync(0xffffffffu, wmax, 16));           // kRowLanes = 16: two rows per instruction
     if (lane == 0) s.cmax_w[warp] = sqrtf(wmax);
@@ -198,52 +175,72 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
 
   if (warp < kLoadWarps) {
     // ------------------------------------------------------------ loaders
-    // The raw fp32 rows of tile t+1 stream into `stage` with cp.async (no registers, thousands of bytes in flight)
-    // while tile t is in the tensor core; once they have landed and the MMA has released the operand buffer they are
-    // split into hi / lo bf16 and written K-major, SWIZZLE_128B.
+    // Rows go global -> registers -> (hi, lo) bf16 -> K-major SWIZZLE_128B operand tile, no staging copy: with two operand
+    // buffers the loaders run a whole tile ahead of the tensor core, and a warp keeps eight 512-byte row loads in flight.
     int it = 0;
     for (int t = part; t < a.n_tiles; t += a.ctas_per_group, ++it) {
-      const uint32_t ph = (uint32_t)it & 1u;
+      const int ab = it & 1;
+      const uint32_t aph = (uint32_t)(it >> 1) & 1u;
       const long long row0 = (long long)t * a.rows_per_tile;
       const int nrows = (int)min((long long)a.rows_per_tile, total_rows - row0);
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      asm volatile("bar.sync 1, 128;" ::: "memory");        // every loader thread's copies have landed
-      if (warp == 0) stamp(0);                               // rows landed
-      pt::mbar_wait(&s.a_empty, ph ^ 1);                    // the MMAs of the previous tile have read the operands
+      const int b0 = (int)(row0 / W), w0 = (int)(row0 % W);
+      pt::mbar_wait(&s.a_empty[ab], aph ^ 1);               // the MMAs that last read this operand buffer are done
       if (warp == 0) stamp(0);                               // operand buffer free
-      uint8_t* hi = s.a_ops[0];
-      uint8_t* lo = s.a_ops[1];
-      float* sx2 = s.sx2[it & 3];        // 4-deep: a slot is rewritten only after the scan of that tile has retired
+      uint8_t* hi = s.a_ops[ab][0];
+      uint8_t* lo = s.a_ops[ab][1];
+      float* sxp = &s.sx2p[it & 3][0][0];   // 4-deep: a slot is rewritten only after the scan of that tile has retired
       if (a.rows_fast) {
-#pragma unroll 4
-        for (int r = warp * kRowsPerInstr + sub_row; r < kTileRows; r += kLoadWarps * kRowsPerInstr) {
-          float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (r < nrows) x = *reinterpret_cast<const float4*>(&s.stage[r * kD + sub_col]);
-          const float sq = row_sum<kRowLanes>(fmaf(x.w, x.w, fmaf(x.z, x.z, fmaf(x.y, x.y, x.x * x.x))));
-          if (sub_col == 0) sx2[r] = sq;
-          split_store4(hi, lo, r, sub_col, x);
+        constexpr int kBatch = 8;                            // row loads in flight per lane
+        constexpr int kRowStep = kLoadWarps * kRowsPerInstr;
+        // (warp-uniform trip count: with two rows per instruction the lanes of a warp hold different rows, and the
+        // shuffles below need the whole warp)
+        for (int rb0 = warp * kRowsPerInstr; rb0 < nrows; rb0 += kBatch * kRowStep) {
+          const int rb = rb0 + sub_row;
+          float4 x[kBatch];
+#pragma unroll
+          for (int i = 0; i < kBatch; ++i) {
+            const int r = rb + i * kRowStep;
+            x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r < nrows) {
+              const int q = w0 + r, b = b0 + q / W, w = q % W;
+              x[i] = __ldg(reinterpret_cast<const float4*>(a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD + sub_col));
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < kBatch; ++i) {
+            const int r = rb + i * kRowStep;
+            float sq = fmaf(x[i].w, x[i].w, fmaf(x[i].z, x[i].z, fmaf(x[i].y, x[i].y, x[i].x * x[i].x)));
+            sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+            sq += __shfl_xor_sync(0xffffffffu, sq, 2);
+            if (r < nrows) {                                 // (rows beyond the tile keep stale operands: never read back)
+              if ((lane & 3) == 0) sxp[((lane % kRowLanes) >> 2) * kTileRows + r] = sq;
+              split_store4(hi, lo, r, sub_col, x[i]);
+            }
+          }
         }
       } else {
-        const int r = tid;
-        const bool live = r < nrows;
-        float sq = 0.f;
-#pragma unroll 4
-        for (int c8 = 0; c8 < kD / 8; ++c8) {
-          float v[8];
+        // channel-first z: lanes = consecutive rows (w contiguous in memory); the two halves of the loader threads split k
+        const int r = tid & (kTileRows - 1), kh = tid >> 7;
+        if (r < nrows) {
+          const int q = w0 + r, b = b0 + q / W, w = q % W;
+          const float* prow = a.z + (long long)b * a.zs_b + (long long)w * a.zs_w + (size_t)g * kD * a.zs_c;
+          float sq = 0.f;
+#pragma unroll 2
+          for (int c8 = kh * (kD / 16); c8 < (kh + 1) * (kD / 16); ++c8) {
+            float v[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = live ? s.stage[(c8 * 8 + i) * kTileRows + r] : 0.f;
+            for (int i = 0; i < 8; ++i) v[i] = __ldg(prow + (size_t)(c8 * 8 + i) * a.zs_c);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) sq = fmaf(v[i], v[i], sq);
-          split_store(hi, lo, (c8 >> 3) * kAtomBytes + pt::sw128_offset(r, c8 & 7), v);
+            for (int i = 0; i < 8; ++i) sq = fmaf(v[i], v[i], sq);
+            split_store(hi, lo, (c8 >> 3) * kAtomBytes + pt::sw128_offset(r, c8 & 7), v);
+          }
+          sxp[kh * kTileRows + r] = sq;
         }
-        sx2[r] = sq;
       }
       pt::fence_async_smem();                                // generic-proxy smem writes -> tensor-core proxy
-      asm volatile("bar.sync 1, 128;" ::: "memory");        // everyone is done reading `stage`
-      if (lane == 0) pt::mbar_arrive(&s.a_full);
+      __syncwarp();
+      if (lane == 0) pt::mbar_arrive(&s.a_full[ab]);
       if (warp == 0) stamp(0);                               // converted
-      const int nt = t + a.ctas_per_group;
-      if (nt < a.n_tiles) prefetch(nt);
     }
   } else if (warp == kLoadWarps) {
     // ------------------------------------------------------------ MMA issuer: D = Ahi*Bhi^T + Ahi*Blo^T + Alo*Bhi^T
@@ -254,11 +251,11 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       for (int t = part; t < a.n_tiles; t += a.ctas_per_group, ++it) {
         const int buf = it & 1;                              // TMEM accumulator stage
         const uint32_t ph = (uint32_t)(it >> 1) & 1u;
-        pt::mbar_wait(&s.a_full, (uint32_t)it & 1u);
+        pt::mbar_wait(&s.a_full[buf], ph);                   // operand buffer and accumulator stage share the parity
         pt::mbar_wait(&s.t_empty[buf], ph ^ 1);
         pt::tc_fence_after();
         stamp(1);                                            // operands + accumulator ready
-        const uint32_t a_hi = pt::smem_u32(s.a_ops[0]), a_lo = pt::smem_u32(s.a_ops[1]);
+        const uint32_t a_hi = pt::smem_u32(s.a_ops[buf][0]), a_lo = pt::smem_u32(s.a_ops[buf][1]);
         const uint32_t pa[3] = {a_hi, a_hi, a_lo}, pb[3] = {b_hi, b_lo, b_hi};
         uint32_t acc = 0;
 #pragma unroll
@@ -271,7 +268,7 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
           }
         }
         pt::umma_commit(&s.t_full[buf]);
-        pt::umma_commit(&s.a_empty);
+        pt::umma_commit(&s.a_empty[buf]);
         stamp(1);                                            // issued
       }
     }
@@ -324,7 +321,12 @@ __global__ void __launch_bounds__(kThreads, 1) pq_search_kernel(PqArgs a) {
       int bi;
       if (mb1 < ma1 || (mb1 == ma1 && ib < ia)) { best = mb1; bi = ib; second = fminf(ma1, mb2); }
       else { best = ma1; bi = ia; second = fminf(mb1, ma2); }
-      const float band = 2.f * kBand * sqrtf(s.sx2[it & 3][r]) * cmax + 4e-7f * fabsf(best);
+      float x2 = 0.f;
+      {
+        const int nparts = a.rows_fast ? kRowLanes / 4 : 2;
+        for (int pp = 0; pp < nparts; ++pp) x2 += s.sx2p[it & 3][pp][r];
+      }
+      const float band = 2.f * kBand * sqrtf(x2) * cmax + 4e-7f * fabsf(best);
       // a chunk of a larger codebook re-scores EVERY row: the chunk winners are merged by their fp32 distances
       const bool amb = (r < nrows) && (multi || second - best <= band);
       const unsigned amb_mask = __ballot_sync(0xffffffffu, amb);
