@@ -95,7 +95,7 @@ int pt_pq_gather_conv1x1(const void* idx, int idx_is_i64, const float* table, co
  * W is bf16 [N, taps*C] row-major, accumulation fp32.
  * row(m): b = m / rows_per_sample, t = m % rows_per_sample; rows with t >= t_valid are not stored;
  * element (m, n) is stored at out[b*oss + t*ors + n*ocs] (residual: [b*rss + t*rrs + n]). */
-enum { PT_ACT_NONE = 0, PT_ACT_RELU = 1, PT_ACT_LEAKY = 2, PT_ACT_GATE = 3 };
+enum { PT_ACT_NONE = 0, PT_ACT_RELU = 1, PT_ACT_LEAKY = 2, PT_ACT_GATE = 3, PT_ACT_GELU = 4 /* erf GELU (wav2vec2) */ };
 
 typedef struct pt_gemm_desc {
   const void* a;          /* bf16 activations */
@@ -149,7 +149,8 @@ int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);
  *   q   rows b*Nq + i, head h at columns [h*head_dim, (h+1)*head_dim), row stride q_stride elements
  *   k,v rows b*Nk + j, same column rule, strides k_stride / v_stride
  *   out rows b*Nq + i, row stride out_stride
- * head_dim must be 64, 1 <= Nk <= 1024 (K, V and Q of one (sample, head) must fit in shared memory), Nq <= 1024. */
+ * head_dim must be 64.  Nk <= 256: tcgen05 kernel; up to 1024 keys / queries: K, V, Q of one (sample, head) resident in
+ * shared memory (mma.sync); beyond that (wav2vec2's ~3000 frames per minute of audio) the keys are streamed. */
 int pt_attention(const void* q, long long q_stride, const void* k, long long k_stride, const void* v,
                  long long v_stride, void* out, long long out_stride, int B, int heads, int head_dim, int Nq, int Nk,
                  float scale, void* stream);
@@ -241,6 +242,31 @@ int pt_embed_tokens512(const int* tokens, const float* emb, int n_emb, const dou
  * torch RNG streams that are not reproducible across devices); base_mask_len = floor(N * cos(pi/2 * (step+1)/T)). */
 int pt_maskgit_step(const float* logits, const int* cur_ids, const float* u, const float* gumbel, int* next_ids,
                     int B, int N, int n_codes, int mask_id, int base_mask_len, float temperature, void* stream);
+
+/* ---- wav2vec2 audio features: scripts/demo.py:105-111 -------------------------------------------
+ * `aud_m(**aud_p(audio)).last_hidden_state` (transformers' Wav2Vec2Model, wav2vec2-base geometry; the reference's own
+ * copy of the model is nets/spg/wav2vec.py:64-151) followed by data_utils/utils.py:14-16 linear_interpolation.
+ *
+ * pt_w2v_frontend: the processor's zero-mean / unit-variance normalisation (eps 1e-7, population variance) + feature
+ * encoder layer 0 (Conv1d(1, 512, 10, stride 5, no bias) -> GroupNorm(512, 512, eps 1e-5) -> GELU) in one pass.
+ *   wave [B, L] fp32 (all utterances of a call have the same length; the reference runs batch 1),  conv0_w [512, 10],
+ *   out bf16 rows [B, out_rows_per_sample, 512], rows t < T0 = (L - 10) / 5 + 1 written.  workspace: see _bytes(B). */
+long long pt_w2v_frontend_workspace_bytes(int B);
+int pt_w2v_frontend(const float* wave, int B, long long L, const float* conv0_w, const float* gn_gamma,
+                    const float* gn_beta, void* out_bf16, long long out_rows_per_sample, void* workspace,
+                    long long workspace_bytes, void* stream);
+
+/* F.interpolate(x.transpose(1, 2), size = Tout, mode = 'linear') of token-major rows: in [B, in_rows_per_sample, C]
+ * (bf16, or fp32 when in_f32), rows t < Tin used -> out [B, C, Tout] fp32 (data_utils/utils.py:14-16). */
+int pt_w2v_interp(const void* in, int in_f32, long long in_rows_per_sample, int B, int Tin, int C, float* out,
+                  int Tout, void* stream);
+
+/* out = LayerNorm_C(in + residual) over rows of C bf16 values (C a multiple of 128, at most 1024), fp32 statistics:
+ * wav2vec2's feature-projection LayerNorm(512) and the post-norm LayerNorm(768)s of its encoder
+ * (transformers modeling_wav2vec2 Wav2Vec2EncoderLayer / nets/spg/wav2vec.py).  residual NULL or bf16 [M, C]; out may
+ * alias in or residual. */
+int pt_layernorm_rows(const void* in_bf16, const void* residual_bf16, const float* gamma, const float* beta, float eps,
+                      void* out_bf16, int M, int C, void* stream);
 
 #ifdef __cplusplus
 }

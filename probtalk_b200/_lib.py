@@ -80,6 +80,13 @@ SIGNATURES = {
                                      C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "pt_maskgit_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                   C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
+    "pt_w2v_frontend_workspace_bytes": (C.c_longlong, [C.c_int]),
+    "pt_w2v_frontend": (C.c_int, [C.c_void_p, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p]),
+    "pt_w2v_interp": (C.c_int, [C.c_void_p, C.c_int, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                C.c_void_p]),
+    "pt_layernorm_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_int,
+                                    C.c_int, C.c_void_p]),
 }
 
 

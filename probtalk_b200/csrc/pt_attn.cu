@@ -196,13 +196,151 @@ __global__ void __launch_bounds__(kWarps * 32, 2) attention_kernel(AttnArgs a, i
   cp_async_wait<0>();
 }
 
+// ---------------------------------------------------------------------------------------------
+// Long sequences (wav2vec2 encoder: ~3000 frames of a minute of audio attend to each other): K and V no longer fit in
+// shared memory, so a CTA owns 128 queries of one (sample, head) and STREAMS the keys through two cp.async buffers of 64
+// keys while the same online-softmax / mma.sync inner block as above consumes the other buffer.
+constexpr int kLWarps = 8, kLQ = kLWarps * 16, kLTile = 64;
+
+__global__ void __launch_bounds__(kLWarps * 32, 2) attention_long_kernel(AttnArgs a, int q_blocks) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(smem_raw);            // [128][72]
+  __nv_bfloat16* KV = Qs + kLQ * kRowPad;                                     // [2 buffers][K | V][64][72]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int qb = blockIdx.x % q_blocks, bh = blockIdx.x / q_blocks;
+  const int b = bh / a.heads, h = bh % a.heads;
+  const int q0 = qb * kLQ;
+  const __nv_bfloat16* kg = a.k + (size_t)b * a.Nk * a.k_stride + h * kHeadDim;
+  const __nv_bfloat16* vg = a.v + (size_t)b * a.Nk * a.v_stride + h * kHeadDim;
+  const __nv_bfloat16* qg = a.q + (size_t)b * a.Nq * a.q_stride + h * kHeadDim;
+  auto stage_kv = [&](int tile, int buf) {
+    __nv_bfloat16* Ks = KV + (size_t)buf * 2 * kLTile * kRowPad;
+    __nv_bfloat16* Vs = Ks + kLTile * kRowPad;
+    for (int i = tid; i < kLTile * 8; i += kLWarps * 32) {
+      const int r = i >> 3, c = (i & 7) * 8, key = tile * kLTile + r;
+      const bool ok = key < a.Nk;
+      const size_t rr = ok ? key : 0;
+      cp_async16(Ks + r * kRowPad + c, kg + rr * a.k_stride + c, ok);
+      cp_async16(Vs + r * kRowPad + c, vg + rr * a.v_stride + c, ok);
+    }
+  };
+  for (int i = tid; i < kLQ * 8; i += kLWarps * 32) {
+    const int r = i >> 3, c = (i & 7) * 8;
+    const bool ok = q0 + r < a.Nq;
+    cp_async16(Qs + r * kRowPad + c, qg + (size_t)(ok ? q0 + r : 0) * a.q_stride + c, ok);
+  }
+  stage_kv(0, 0);
+  cp_async_commit();
+  const int n_tiles = (a.Nk + kLTile - 1) / kLTile;
+  const int g = lane >> 2, tig = lane & 3;
+  uint32_t qf[4][4];
+  float mx0 = -INFINITY, mx1 = -INFINITY, sum0 = 0.f, sum1 = 0.f;
+  float oacc[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) oacc[nt][0] = oacc[nt][1] = oacc[nt][2] = oacc[nt][3] = 0.f;
+  for (int tile = 0; tile < n_tiles; ++tile) {
+    const int buf = tile & 1;
+    if (tile + 1 < n_tiles) { stage_kv(tile + 1, buf ^ 1); cp_async_commit(); cp_async_wait<1>(); }
+    else cp_async_wait<0>();
+    __syncthreads();
+    if (tile == 0) {
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const __nv_bfloat16* qp = Qs + (warp * 16 + g) * kRowPad + ks * 16 + tig * 2;
+        qf[ks][0] = *reinterpret_cast<const uint32_t*>(qp);
+        qf[ks][1] = *reinterpret_cast<const uint32_t*>(qp + 8 * kRowPad);
+        qf[ks][2] = *reinterpret_cast<const uint32_t*>(qp + 8);
+        qf[ks][3] = *reinterpret_cast<const uint32_t*>(qp + 8 * kRowPad + 8);
+      }
+    }
+    const __nv_bfloat16* Ks = KV + (size_t)buf * 2 * kLTile * kRowPad;
+    const __nv_bfloat16* Vs = Ks + kLTile * kRowPad;
+#pragma unroll
+    for (int kb = 0; kb < kLTile; kb += kKeyBlock) {
+      const int key0 = tile * kLTile + kb;
+      if (key0 >= a.Nk) break;                                   // block-uniform
+      float sacc[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const __nv_bfloat16* kp = Ks + (kb + nt * 8 + g) * kRowPad + ks * 16 + tig * 2;
+          mma_bf16(sacc[nt], qf[ks], *reinterpret_cast<const uint32_t*>(kp), *reinterpret_cast<const uint32_t*>(kp + 8));
+        }
+      }
+      float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int key = key0 + nt * 8 + tig * 2;
+        if (key >= a.Nk) { sacc[nt][0] = -INFINITY; sacc[nt][2] = -INFINITY; }
+        if (key + 1 >= a.Nk) { sacc[nt][1] = -INFINITY; sacc[nt][3] = -INFINITY; }
+        bm0 = fmaxf(bm0, fmaxf(sacc[nt][0], sacc[nt][1]));
+        bm1 = fmaxf(bm1, fmaxf(sacc[nt][2], sacc[nt][3]));
+      }
+      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1)); bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1)); bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+      const float nm0 = fmaxf(mx0, bm0), nm1 = fmaxf(mx1, bm1);     // finite: a processed block holds a valid key
+      const float sc0 = exp2f((mx0 - nm0) * a.scale_log2e), sc1 = exp2f((mx1 - nm1) * a.scale_log2e);
+      mx0 = nm0; mx1 = nm1;
+      sum0 *= sc0; sum1 *= sc1;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) { oacc[nt][0] *= sc0; oacc[nt][1] *= sc0; oacc[nt][2] *= sc1; oacc[nt][3] *= sc1; }
+      uint32_t pf[4][2];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const float p0 = exp2f((sacc[nt][0] - mx0) * a.scale_log2e), p1 = exp2f((sacc[nt][1] - mx0) * a.scale_log2e);
+        const float p2 = exp2f((sacc[nt][2] - mx1) * a.scale_log2e), p3 = exp2f((sacc[nt][3] - mx1) * a.scale_log2e);
+        sum0 += p0 + p1; sum1 += p2 + p3;
+        pf[nt][0] = pt::pack_bf16x2(p0, p1);
+        pf[nt][1] = pt::pack_bf16x2(p2, p3);
+      }
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+        const uint32_t af[4] = {pf[2 * kt][0], pf[2 * kt][1], pf[2 * kt + 1][0], pf[2 * kt + 1][1]};
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+          uint32_t bf[4];
+          const __nv_bfloat16* vp = Vs + (kb + kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * kRowPad + np * 16 + (lane >> 4) * 8;
+          ldmatrix_x4_trans(bf, vp);
+          mma_bf16(oacc[2 * np], af, bf[0], bf[1]);
+          mma_bf16(oacc[2 * np + 1], af, bf[2], bf[3]);
+        }
+      }
+    }
+    __syncthreads();                                     // everyone is done with `buf` before it is refilled
+  }
+  sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+  sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+  const float inv0 = 1.f / sum0, inv1 = 1.f / sum1;
+  const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+  __nv_bfloat16* o0 = a.out + ((size_t)b * a.Nq + r0) * a.out_stride + h * kHeadDim + tig * 2;
+  __nv_bfloat16* o1 = a.out + ((size_t)b * a.Nq + r1) * a.out_stride + h * kHeadDim + tig * 2;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    if (r0 < a.Nq) *reinterpret_cast<uint32_t*>(o0 + nt * 8) = pt::pack_bf16x2(oacc[nt][0] * inv0, oacc[nt][1] * inv0);
+    if (r1 < a.Nq) *reinterpret_cast<uint32_t*>(o1 + nt * 8) = pt::pack_bf16x2(oacc[nt][2] * inv1, oacc[nt][3] * inv1);
+  }
+}
+
+int launch_attn_long(const AttnArgs& a, int B, cudaStream_t st) {
+  const size_t smem = (size_t)(kLQ + 4 * kLTile) * kRowPad * sizeof(__nv_bfloat16);      // 55 296 bytes
+  PT_SMEM_OPT_IN(attention_long_kernel, smem);
+  const int q_blocks = (a.Nq + kLQ - 1) / kLQ;
+  const long long grid = (long long)B * a.heads * q_blocks;
+  if (grid > 0x7fffffffLL) return pt::fail("pt_attention: too many (sample, head, query block) units");
+  attention_long_kernel<<<(unsigned)grid, kLWarps * 32, smem, st>>>(a, q_blocks);
+  PT_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int launch_attn(const AttnArgs& a, int B, cudaStream_t st) {
   const int NQP = (a.Nq + 15) & ~15;
   const int NKP = ((a.Nk + kKeyBlock - 1) / kKeyBlock) * kKeyBlock;
   const size_t one = (size_t)(2 * NKP + NQP) * kRowPad * sizeof(__nv_bfloat16);
   const int nbuf = (2 * one <= 226 * 1024) ? 2 : 1;
   const size_t smem = nbuf * one;
-  if (smem > 226 * 1024) return pt::fail("pt_attention: Nq=%d Nk=%d do not fit in shared memory", a.Nq, a.Nk);
+  if (smem > 226 * 1024) return launch_attn_long(a, B, st);           // K, V, Q of a head no longer fit: stream the keys
   if (smem > 48 * 1024) PT_SMEM_OPT_IN(attention_kernel, smem);
   const int sms = pt::sm_count();
   int per_sm = (int)((227 * 1024) / (smem + 1024));
@@ -222,8 +360,7 @@ extern "C" int pt_attention(const void* q, long long q_stride, const void* k, lo
   if (B <= 0 || Nq <= 0) return 0;
   if (!q || !k || !v || !out) return pt::fail("pt_attention: null pointer");
   if (head_dim != kHeadDim) return pt::fail("pt_attention: only head_dim 64 is built (got %d)", head_dim);
-  if (Nk <= 0 || Nk > 1024) return pt::fail("pt_attention: 1..1024 keys per head supported (got %d)", Nk);
-  if (Nq > 1024) return pt::fail("pt_attention: at most 1024 queries per sample (got %d)", Nq);
+  if (Nk <= 0) return pt::fail("pt_attention: need at least one key (got %d)", Nk);
   if ((q_stride | k_stride | v_stride) & 7) return pt::fail("pt_attention: row strides must be multiples of 8 elements");
   if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15)
     return pt::fail("pt_attention: q/k/v must be 16-byte aligned");
@@ -243,5 +380,6 @@ extern "C" int pt_attention(const void* q, long long q_stride, const void* k, lo
   a.heads = heads; a.Nq = Nq; a.Nk = Nk;
   a.scale_log2e = scale * 1.4426950408889634f;
   cudaStream_t st = (cudaStream_t)stream;
+  if (Nk > 1024 || Nq > 1024) return launch_attn_long(a, B, st);      // K / V streamed through shared memory
   return launch_attn(a, B, st);
 }

@@ -323,6 +323,54 @@ __global__ void ln_kernel(const InT* __restrict__ in, const __nv_bfloat16* __res
   }
 }
 
+// nn.LayerNorm over C = 128 * kVec channels of bf16 rows (+ bf16 residual), one warp per row: the 768-wide norms of the
+// wav2vec2 encoder (feature projection, encoder.layer_norm, layer_norm / final_layer_norm of every layer)
+template <int kVec>
+__global__ void ln_rows_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ res,
+                               const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                               __nv_bfloat16* __restrict__ out, int M) {
+  constexpr int C = 128 * kVec;
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= M) return;
+  float v[4 * kVec];
+  const uint2* p = reinterpret_cast<const uint2*>(in + (size_t)row * C);
+  const uint2* pr = res ? reinterpret_cast<const uint2*>(res + (size_t)row * C) : nullptr;
+#pragma unroll
+  for (int i = 0; i < kVec; ++i) {
+    const uint2 x = __ldg(p + lane + 32 * i);
+    const __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&x.x), h1 = *reinterpret_cast<const __nv_bfloat162*>(&x.y);
+    v[4 * i] = __bfloat162float(h0.x); v[4 * i + 1] = __bfloat162float(h0.y);
+    v[4 * i + 2] = __bfloat162float(h1.x); v[4 * i + 3] = __bfloat162float(h1.y);
+    if (pr) {
+      const uint2 y = __ldg(pr + lane + 32 * i);
+      const __nv_bfloat162 g0 = *reinterpret_cast<const __nv_bfloat162*>(&y.x), g1 = *reinterpret_cast<const __nv_bfloat162*>(&y.y);
+      v[4 * i] += __bfloat162float(g0.x); v[4 * i + 1] += __bfloat162float(g0.y);
+      v[4 * i + 2] += __bfloat162float(g1.x); v[4 * i + 3] += __bfloat162float(g1.y);
+    }
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4 * kVec; ++i) s += v[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s * (1.f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4 * kVec; ++i) { const float d = v[i] - mean; q = fmaf(d, d, q); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q * (1.f / C) + eps);
+#pragma unroll
+  for (int i = 0; i < kVec; ++i) {
+    const int c = 4 * (lane + 32 * i);
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c)), bb = __ldg(reinterpret_cast<const float4*>(beta + c));
+    const float y0 = (v[4 * i] - mean) * rstd * g.x + bb.x, y1 = (v[4 * i + 1] - mean) * rstd * g.y + bb.y;
+    const float y2 = (v[4 * i + 2] - mean) * rstd * g.z + bb.z, y3 = (v[4 * i + 3] - mean) * rstd * g.w + bb.w;
+    *reinterpret_cast<uint2*>(out + (size_t)row * C + c) = make_uint2(pt::pack_bf16x2(y0, y1), pt::pack_bf16x2(y2, y3));
+  }
+}
+
 // StylizationBlock_V3 'sb' branch up to the output Linear (PTransformer.py:134-139):
 //   out = SiLU( LN(h) * (1 + scale[label]) + shift[label] ),  mod = [n_classes, 1024] = [scale | shift]
 template <typename InT>
@@ -533,6 +581,30 @@ extern "C" int pt_layernorm512(const void* in, int in_f32, const void* residual_
     ln_kernel<float><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const float*)in, res, rlo, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M);
   else
     ln_kernel<__nv_bfloat16><<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, res, rlo, gamma, beta, out_f32, (__nv_bfloat16*)out_bf16, (__nv_bfloat16*)out_lo, M);
+  PT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int pt_layernorm_rows(const void* in_bf16, const void* residual_bf16, const float* gamma, const float* beta,
+                                 float eps, void* out_bf16, int M, int C, void* stream) {
+  if (M <= 0) return 0;
+  if (!in_bf16 || !gamma || !beta || !out_bf16) return pt::fail("pt_layernorm_rows: null pointer");
+  if (C < 128 || C > 1024 || (C & 127)) return pt::fail("pt_layernorm_rows: C must be a multiple of 128 in [128, 1024] (got %d)", C);
+  const __nv_bfloat16* in = (const __nv_bfloat16*)in_bf16;
+  const __nv_bfloat16* res = (const __nv_bfloat16*)residual_bf16;
+  __nv_bfloat16* out = (__nv_bfloat16*)out_bf16;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int blocks = (M + 7) / 8;
+  switch (C / 128) {
+    case 1: ln_rows_kernel<1><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    case 2: ln_rows_kernel<2><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    case 3: ln_rows_kernel<3><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    case 4: ln_rows_kernel<4><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    case 5: ln_rows_kernel<5><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    case 6: ln_rows_kernel<6><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    case 7: ln_rows_kernel<7><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+    default: ln_rows_kernel<8><<<blocks, 256, 0, st>>>(in, res, gamma, beta, eps, out, M); break;
+  }
   PT_CUDA(cudaGetLastError());
   return 0;
 }

@@ -83,6 +83,7 @@ struct GemmKernelArgs {
 __device__ __forceinline__ float apply_act(float v, int act, float slope) {
   if (act == PT_ACT_RELU) return fmaxf(v, 0.f);
   if (act == PT_ACT_LEAKY) return v > 0.f ? v : v * slope;
+  if (act == PT_ACT_GELU) return 0.5f * v * (1.f + erff(v * 0.70710678118654752f));      // exact (erf) GELU, nn.GELU()
   return v;
 }
 

@@ -20,7 +20,7 @@ import torch
 from . import _lib
 from ._lib import GemmDesc, check
 from . import ops
-from .ops import ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_GATE
+from .ops import ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_GATE, ACT_GELU
 
 BF16 = torch.bfloat16
 F32 = torch.float32

@@ -12,7 +12,7 @@ import torch
 from . import _lib
 from ._lib import GemmDesc, check
 
-ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_GATE = 0, 1, 2, 3
+ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_GATE, ACT_GELU = 0, 1, 2, 3, 4
 
 
 def _stream() -> int:
@@ -199,3 +199,55 @@ def pq_ema_update(z, idx, codebooks, ema_dw, ema_cluster_size, decay, epsilon, s
                              ema_cluster_size.data_ptr(), float(decay), float(epsilon), int(step), mse.data_ptr(),
                              dead.data_ptr(), ws.data_ptr(), nbytes, _stream()), "pt_pq_ema_update")
     return mse, dead
+
+
+def attention(q, k, v, B, Nq, Nk, heads=8, head_dim=64, scale=None):
+    """bf16 attention core (pt_attention): q [B*Nq, heads*head_dim], k / v [B*Nk, ...] bf16 (any row stride that is a
+    multiple of 8) -> bf16 [B*Nq, heads*head_dim].  Nk <= 256: tcgen05; beyond what fits on chip the keys are streamed."""
+    _need_cuda(q, k, v)
+    assert q.dtype == k.dtype == v.dtype == torch.bfloat16
+    out = torch.empty(B * Nq, heads * head_dim, dtype=torch.bfloat16, device=q.device)
+    scale = scale if scale is not None else head_dim ** -0.5
+    check(_lib.lib().pt_attention(q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+                                  out.data_ptr(), heads * head_dim, B, heads, head_dim, Nq, Nk, scale, _stream()),
+          "pt_attention")
+    return out
+
+
+def layernorm_rows(x, residual, gamma, beta, eps=1e-5, out=None):
+    """LayerNorm over bf16 rows [M, C] (+ bf16 residual), C a multiple of 128 up to 1024 (pt_layernorm_rows)."""
+    _need_cuda(x, residual, gamma, beta)
+    assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.is_contiguous()
+    assert gamma.dtype == beta.dtype == torch.float32
+    M, Cc = x.shape
+    out = torch.empty_like(x) if out is None else out
+    check(_lib.lib().pt_layernorm_rows(x.data_ptr(), _ptr(residual), gamma.data_ptr(), beta.data_ptr(), float(eps),
+                                       out.data_ptr(), M, Cc, _stream()), "pt_layernorm_rows")
+    return out
+
+
+def w2v_frontend(wave, conv0_w, gn_gamma, gn_beta):
+    """wav2vec2 processor normalisation + conv0 + GroupNorm + GELU (pt_w2v_frontend): wave [B, L] fp32 ->
+    bf16 rows [B, T0, 512], T0 = (L - 10) // 5 + 1."""
+    _need_cuda(wave, conv0_w, gn_gamma, gn_beta)
+    assert wave.dtype == torch.float32 and wave.dim() == 2 and wave.is_contiguous()
+    B, L = wave.shape
+    T0 = (L - 10) // 5 + 1
+    lib = _lib.lib()
+    nbytes = lib.pt_w2v_frontend_workspace_bytes(B)
+    ws = torch.empty((nbytes + 7) // 8, dtype=torch.float64, device=wave.device)
+    out = torch.empty(B, max(T0, 0), 512, dtype=torch.bfloat16, device=wave.device)
+    check(lib.pt_w2v_frontend(wave.data_ptr(), B, L, conv0_w.data_ptr(), gn_gamma.data_ptr(), gn_beta.data_ptr(),
+                              out.data_ptr(), max(T0, 0), ws.data_ptr(), nbytes, _stream()), "pt_w2v_frontend")
+    return out
+
+
+def w2v_interp(rows, t_out):
+    """rows [B, T, C] (bf16 / fp32) -> F.interpolate(rows.transpose(1, 2), size=t_out, mode='linear') as fp32 [B, C, t_out]."""
+    _need_cuda(rows)
+    assert rows.dim() == 3 and rows.is_contiguous() and rows.dtype in (torch.bfloat16, torch.float32)
+    B, T, Cc = rows.shape
+    out = torch.empty(B, Cc, t_out, dtype=torch.float32, device=rows.device)
+    check(_lib.lib().pt_w2v_interp(rows.data_ptr(), int(rows.dtype == torch.float32), T, B, T, Cc, out.data_ptr(), t_out,
+                                   _stream()), "pt_w2v_interp")
+    return out

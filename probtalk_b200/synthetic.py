@@ -87,3 +87,51 @@ def synthetic_audio(B, T, seed):
     """wav2vec2-shaped per-frame features [B, 768, T] ~ N(0, 1)."""
     g = torch.Generator(device="cpu").manual_seed(seed)
     return torch.randn(B, AUDIO_DIM, T, generator=g)
+
+
+def make_wav2vec2(seed=11):
+    """A transformers ``Wav2Vec2Model`` of wav2vec2-base geometry (the architecture scripts/demo.py:76-77 downloads as
+    facebook/wav2vec2-base-960h; no network here) with every tensor drawn from a seeded CPU generator: fan-in scaled
+    weights (He gain for the GELU convolutions), LayerNorm / GroupNorm gains in [0.5, 1.5), small biases.  The library's
+    own init (std 0.02 Linears) would leave every encoder layer close to x = LN(x) and hide attention / FF bugs."""
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    model = Wav2Vec2Model(Wav2Vec2Config()).eval()
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    sd = model.state_dict()
+    new = {}
+    for k, v in sd.items():
+        shape = tuple(v.shape)
+        if k.endswith("parametrizations.weight.original0"):
+            continue                                                  # set from original1 below
+        if "layer_norm.weight" in k:
+            new[k] = torch.rand(shape, generator=g) + 0.5
+        elif k.endswith(".bias"):
+            new[k] = torch.randn(shape, generator=g) * 0.05
+        elif k.endswith("parametrizations.weight.original1"):
+            vv = torch.randn(shape, generator=g) * (2.0 / math.sqrt(shape[1] * shape[2]))
+            new[k] = vv
+            gain = torch.rand(1, 1, shape[2], generator=g) + 0.5
+            new[k.replace("original1", "original0")] = vv.norm(dim=(0, 1), keepdim=True) * gain
+        elif len(shape) == 3:
+            new[k] = torch.randn(shape, generator=g) * math.sqrt(2.0 / (shape[1] * shape[2]))
+        elif len(shape) == 2:
+            new[k] = torch.randn(shape, generator=g) / math.sqrt(shape[1])
+        else:
+            new[k] = torch.randn(shape, generator=g) * 0.05
+    model.load_state_dict(new, strict=True)
+    return model
+
+
+def synthetic_waveform(B, L, seed, sr=16000):
+    """[B, L] fp32 'speech-like' audio: a few drifting harmonics under a slow envelope plus a noise floor, peak ~0.3."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    t = torch.arange(L, dtype=torch.float64) / sr
+    out = torch.zeros(B, L, dtype=torch.float64)
+    for b in range(B):
+        f0 = 90.0 + 120.0 * torch.rand(1, generator=g).item()
+        env = 0.55 + 0.45 * torch.sin(2 * math.pi * (1.5 + torch.rand(1, generator=g).item() * 3.0) * t)
+        for h in range(1, 7):
+            ph = 2 * math.pi * torch.rand(1, generator=g).item()
+            out[b] += env * torch.sin(2 * math.pi * f0 * h * t * (1.0 + 0.01 * torch.sin(2 * math.pi * 0.7 * t)) + ph) / (h * 6.0)
+        out[b] += 0.02 * torch.randn(L, generator=g, dtype=torch.float64)
+    return out.float()
