@@ -498,6 +498,46 @@ def run_extras(args, E, S, states, weights, dev, world, rank):
     out["cfg5"] = {"utterances_per_s": n_utt / (ms * 1e-3), "frames_per_s": n_utt * 1800 / (ms * 1e-3), "ms": ms,
                    "utterances": n_utt, "utterances_per_gpu": Bu, "frames": 1800,
                    "what": "windows_demo: 12 predictor windows + one decode + 13 refiner windows per utterance"}
+    del pipe, a5
+    torch.cuda.empty_cache()
+    # ---- f1: wav2vec2-base features of 60 s utterances (scripts/demo.py:105-111), 8 utterances per GPU
+    # per call; random-init weights of the architecture (the checkpoint is not on the box); the reference's own
+    # implementation (transformers, fp32) timed on the host cores for a bounded 10 s sample
+    try:
+        from probtalk_b200 import audio as A
+        model = S.make_wav2vec2(11)
+        WW = A.Wav2VecWeights(model.state_dict(), dev)
+        Bw, Lw = 8, 60 * 16000
+        wplan = A.Wav2VecPlan(WW, Bw, Lw)
+        wave = S.synthetic_waveform(1, Lw, 5).to(dev).repeat(Bw, 1).contiguous()
+        ms = _max_over_ranks(_time_steps(lambda: wplan.run(wave), 5, warm=3), dev, world)
+        out["f1_wav2vec2"] = {"audio_seconds_per_s": world * Bw * 60.0 / (ms * 1e-3), "ms": ms, "utterances_per_gpu": Bw,
+                              "seconds_per_utterance": 60.0, "frames_50fps": wplan.T, "frames_30fps": wplan.t_out,
+                              "launches": wplan.launches, "tflops": wplan.flops / (ms * 1e-3) / 1e12,
+                              "what": "processor normalisation + Wav2Vec2Model.last_hidden_state + linear interpolation to 30 fps, bf16"}
+        del wplan, wave
+        if rank == 0:
+            feats = A.Wav2Vec2Features(WW)
+            hw = S.synthetic_waveform(1, Lw, 6)[0].pin_memory()
+            feats(hw)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(5):
+                feats(hw).cpu()
+            out["f1_wav2vec2"]["e2e_ms_one_utterance_host_to_host"] = (time.perf_counter() - t0) / 5 * 1e3
+            xs = S.synthetic_waveform(1, 10 * 16000, 7)
+            xs = (xs - xs.mean()) / torch.sqrt(xs.var(unbiased=False) + 1e-7)
+            with torch.no_grad():
+                model(xs)
+                t0 = time.perf_counter()
+                model(xs)
+                dt = time.perf_counter() - t0
+            out["f1_wav2vec2"]["cpu_reference"] = {"audio_seconds_per_s": 10.0 / dt, "sample": "one 10 s utterance", "threads": torch.get_num_threads(),
+                                                   "kind": "transformers Wav2Vec2Model, fp32, host cores"}
+        del WW, model
+        torch.cuda.empty_cache()
+    except ImportError as e:                      # transformers missing: the row is reported as not run, nothing else changes
+        out["f1_wav2vec2"] = {"unavailable": str(e)}
     return out
 
 
