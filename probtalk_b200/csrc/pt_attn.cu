@@ -16,6 +16,10 @@
 int pt_attention_tc(const void* q, long long q_stride, const void* k, long long k_stride, const void* v,
                     long long v_stride, void* out, long long out_stride, int B, int heads, int Nq, int Nk, float scale,
                     cudaStream_t st);
+// tcgen05 implementation with streamed keys for longer sequences (pt_attn_flash.cu)
+int pt_attention_flash(const void* q, long long q_stride, const void* k, long long k_stride, const void* v,
+                       long long v_stride, void* out, long long out_stride, int B, int heads, int Nq, int Nk, float scale,
+                       cudaStream_t st);
 
 namespace {
 
@@ -372,6 +376,9 @@ extern "C" int pt_attention(const void* q, long long q_stride, const void* k, lo
     if (Nk <= 256 && !legacy)
       return pt_attention_tc(q, q_stride, k, k_stride, v, v_stride, out, out_stride, B, heads, Nq, Nk, scale,
                              (cudaStream_t)stream);
+    if (!legacy)
+      return pt_attention_flash(q, q_stride, k, k_stride, v, v_stride, out, out_stride, B, heads, Nq, Nk, scale,
+                                (cudaStream_t)stream);
   }
   AttnArgs a;
   a.q = (const __nv_bfloat16*)q; a.k = (const __nv_bfloat16*)k; a.v = (const __nv_bfloat16*)v;
