@@ -39,6 +39,7 @@ struct AttnTcArgs {
   int p_bufs;                      // P tiles in smem and O accumulators in TMEM (2 = softmax never waits for the last P V)
   int s_bufs;                      // S accumulators in TMEM (2 = the next unit's Q K^T overlaps this unit's softmax)
   float scale_log2e;
+  long long* trace;                // developer hook (PT_ATTN_TRACE): clock64 stamps of CTA 0, [5 roles][16 units][4]
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -67,6 +68,11 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
   return d;
 }
+
+#define ATRACE(role, unit, ev)                                                                               \
+  do {                                                                                                       \
+    if (a.trace && blockIdx.x == 0 && (unit) < 16) a.trace[((role) * 16 + (unit)) * 4 + (ev)] = clock64();     \
+  } while (0)
 
 template <int kNch>                                     // 1..3: keys / 32, scores stay in registers; 0: two TMEM passes
 __global__ void __launch_bounds__(kThreadsTc, 2)
@@ -148,64 +154,81 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const int mt = u % a.m_tiles, bh = u / a.m_tiles;
         const int h = bh % a.heads, b = bh / a.heads;
         uint8_t* sq = smem + (size_t)sq_i * qk_bytes;
+        ATRACE(0, it, 0);
         pt::mbar_wait(&qk_empty[sq_i], qph ^ 1);
+        ATRACE(0, it, 1);
         pt::mbar_expect_tx(&qk_full[sq_i], (uint32_t)a.q_box * 128u + kv_bytes);
         pt::tma_load_2d(sq, &tmap_q, &qk_full[sq_i], h * 64, b * a.Nq + mt * kQRows);
         pt::tma_load_2d(sq + q_region, &tmap_k, &qk_full[sq_i], h * 64, b * a.Nk);
         pt::mbar_wait(&v_empty[sv_i], vph ^ 1);
         pt::mbar_expect_tx(&v_full[sv_i], kv_bytes);
         pt::tma_load_2d(v_smem + (size_t)sv_i * kv_pad, &tmap_v, &v_full[sv_i], h * 64, b * a.Nk);
+        ATRACE(0, it, 2);
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // ------------------------------------------------------------ MMA issuer of S = Q K^T (warp 2 issues the P V MMAs)
+    // The MMAs of this kernel are short (N <= 256 keys, 16-64 cycles of tensor time each), so the issue path counts.  The
+    // WHOLE warp walks the loop (every lane blocks on the same barriers) and one ELECTED lane issues: under `if (lane ==
+    // 0)` the compiler wraps every tcgen05.mma in an election loop with five R2UR moves and rebuilds both descriptors
+    // (~20 dependent instructions, ~70 cycles per MMA), and one thread polling both queues with mbarrier.test_wait +
+    // __nanosleep added up to ~1000 cycles per group of MMAs (measured on the streamed-key kernel, pt_attn_flash.cu).
+    // S runs ahead of P V as far as the S accumulators and the Q/K slots allow (the barriers say when).
+    {
       const uint32_t idesc_s = pt::umma_idesc_bf16(kQRows, (uint32_t)a.NKP);
+      const int n_my = (n_units > (int)blockIdx.x) ? (n_units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+      for (int is = 0; is < n_my; ++is) {
+        const int st = is % a.qk_stages, sb = is % a.s_bufs;
+        const uint32_t ph = (uint32_t)(is / a.qk_stages) & 1u, sph = (uint32_t)(is / a.s_bufs) & 1u;
+        pt::mbar_wait(&qk_full[st], ph);
+        if (lane == 0) ATRACE(1, is, 0);
+        pt::mbar_wait(&s_free[sb], sph ^ 1);
+        pt::tc_fence_after();
+        if (pt::elect_one()) {
+          ATRACE(1, is, 1);
+          const uint32_t sq = pt::smem_u32(smem + (size_t)st * qk_bytes);
+          const uint64_t dq = pt::umma_desc_sw128(sq), dk = pt::umma_desc_sw128(sq + q_region);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            pt::umma_bf16(tmem_s + sb * a.NKP, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k ? 1u : 0u);
+          pt::umma_commit(&s_full[sb]);
+          pt::umma_commit(&qk_empty[st]);                // Q and K of this slot may be overwritten once S is complete
+          ATRACE(1, is, 2);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 2) {
+    // ------------------------------------------------------------ MMA issuer of O = P V
+    {
       const uint32_t idesc_o = pt::umma_idesc_bf16(kQRows, 64) | (1u << 16);       // B operand (V) is MN-major
-      // Two queues, polled without blocking: S(i) = Q K^T of this CTA's i-th unit, O(j) = P V of its j-th unit.
-      // S runs ahead of P V as far as the S accumulators and the Q/K slots allow (the barriers say when).
       const int n_my = (n_units > (int)blockIdx.x) ? (n_units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
       const int ksteps = a.NKP / 16;
-      int is = 0, ip = 0;
-      uint32_t spins = 0;
-      while (ip < n_my) {
-        bool progressed = false;
-        // P V first: the single P tile and O accumulator gate the next unit's softmax, Q K^T only has to stay ahead
-        if (ip < is) {
-          const int st = ip % a.v_stages;
-          const uint32_t ph = (uint32_t)(ip / a.v_stages) & 1u;
-          const int pb = PB(ip);
-          const uint32_t pph = PPH(ip);
-          // P (bf16) is in smem, the O accumulator's previous contents have been read out of TMEM, V has landed
-          if (pt::mbar_test_wait(P_FULL(pb), pph) && pt::mbar_test_wait(O_FREE(pb), pph ^ 1) && pt::mbar_test_wait(&v_full[st], ph)) {
-            const uint32_t sv = pt::smem_u32(v_smem + (size_t)st * kv_pad);
-            const uint32_t sp = pt::smem_u32(p_smem) + pb * p_bytes;
-            pt::tc_fence_after();
-            for (int j = 0; j < ksteps; ++j)
-              pt::umma_bf16(tmem_o + pb * 64, pt::umma_desc_sw128(sp + (j >> 2) * kAtomBytes + (j & 3) * 32),
-                            pt::umma_desc_sw128_mn(sv + j * 2048), idesc_o, j ? 1u : 0u);
-            pt::umma_commit(O_FULL(pb));
-            pt::umma_commit(&v_empty[st]);
-            ++ip; progressed = true;
+      for (int ip = 0; ip < n_my; ++ip) {
+        const int st = ip % a.v_stages;
+        const uint32_t ph = (uint32_t)(ip / a.v_stages) & 1u;
+        const int pb = PB(ip);
+        const uint32_t pph = PPH(ip);
+        // V has landed, the O accumulator's previous contents have been read out of TMEM, P (bf16) is in smem
+        pt::mbar_wait(&v_full[st], ph);
+        if (lane == 0) ATRACE(2, ip, 0);
+        pt::mbar_wait(O_FREE(pb), pph ^ 1);
+        pt::mbar_wait(P_FULL(pb), pph);
+        pt::tc_fence_after();
+        if (pt::elect_one()) {
+          ATRACE(2, ip, 1);
+          uint64_t dp = pt::umma_desc_sw128(pt::smem_u32(p_smem) + pb * p_bytes);
+          uint64_t dv = pt::umma_desc_sw128_mn(pt::smem_u32(v_smem + (size_t)st * kv_pad));
+          for (int j = 0; j < ksteps; ++j) {
+            pt::umma_bf16(tmem_o + pb * 64, dp, dv, idesc_o, j ? 1u : 0u);
+            dp += ((j & 3) == 3) ? (uint64_t)((kAtomBytes >> 4) - 6) : (uint64_t)2;      // next 16 keys: +32 B, or the next 64-key atom
+            dv += (uint64_t)(2048 >> 4);
           }
+          pt::umma_commit(O_FULL(pb));
+          pt::umma_commit(&v_empty[st]);
+          ATRACE(2, ip, 2);
         }
-        if (is < n_my) {
-          const int st = is % a.qk_stages, sb = is % a.s_bufs;
-          const uint32_t ph = (uint32_t)(is / a.qk_stages) & 1u, sph = (uint32_t)(is / a.s_bufs) & 1u;
-          if (pt::mbar_test_wait(&qk_full[st], ph) && pt::mbar_test_wait(&s_free[sb], sph ^ 1)) {
-            const uint32_t sq = pt::smem_u32(smem + (size_t)st * qk_bytes);
-            const uint32_t sk = sq + q_region;
-            pt::tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              pt::umma_bf16(tmem_s + sb * a.NKP, pt::umma_desc_sw128(sq + k * 32), pt::umma_desc_sw128(sk + k * 32), idesc_s, k ? 1u : 0u);
-            pt::umma_commit(&s_full[sb]);
-            pt::umma_commit(&qk_empty[st]);              // Q and K of this slot may be overwritten once S is complete
-            ++is; progressed = true;
-          }
-        }
-        if (progressed) spins = 0;
-        else { __nanosleep(40); if (++spins > PT_SPIN_LIMIT) __trap(); }   // yield issue slots to the softmax warps
+        __syncwarp();
       }
     }
    }
@@ -223,7 +246,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const int sb = dbl ? (it & 1) : 0;
       const uint32_t sph = (uint32_t)(dbl ? (it >> 1) : it) & 1u;
       const uint32_t tmem_sb = tmem_s + sb * a.NKP;
+      if (q == 0 && lane == 0) ATRACE(3, it, 0);
       pt::mbar_wait(&s_full[sb], sph);
+      if (q == 0 && lane == 0) ATRACE(3, it, 1);
       pt::tc_fence_after();
       // a warp whose 32 rows all lie beyond the last query of this tile (Nq = 88: rows 96..127) only keeps the barrier
       // protocol going; its P rows stay stale, which is harmless because every O row depends on its own P row only
@@ -303,6 +328,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         pt::fence_async_smem();                          // P stores -> visible to the tensor-core proxy
         __syncwarp();
         if (lane == 0) { pt::mbar_arrive(P_FULL(pb)); pt::mbar_arrive(&sums_full[up]); }
+        if (q == 0 && lane == 0) ATRACE(3, it, 2);
         continue;
       }
       // pass 1: row maximum (only the last 32-column chunk can hold keys beyond Nk)
@@ -360,6 +386,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       pt::fence_async_smem();                            // P stores -> visible to the tensor-core proxy
       __syncwarp();
       if (lane == 0) { pt::mbar_arrive(&s_free[sb]); pt::mbar_arrive(P_FULL(pb)); pt::mbar_arrive(&sums_full[up]); }
+      if (q == 0 && lane == 0) ATRACE(3, it, 2);
     }
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
@@ -374,8 +401,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const uint32_t pph = PPH(it);
       const int mt = u % a.m_tiles, bh = u / a.m_tiles;
       const int h = bh % a.heads, b = bh / a.heads;
+      if (q == 0 && lane == 0) ATRACE(4, it, 0);
       pt::mbar_wait(&sums_full[up], (uint32_t)(it >> 1) & 1u);
       pt::mbar_wait(O_FULL(pb), pph);
+      if (q == 0 && lane == 0) ATRACE(4, it, 1);
       pt::tc_fence_after();
       if (q * 32 >= min(kQRows, a.Nq - mt * kQRows)) {   // no query rows here: nothing to read or store
         __syncwarp();
@@ -404,6 +433,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                                          pt::pack_bf16x2(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv));
         }
       }
+      if (q == 0 && lane == 0) ATRACE(4, it, 2);
     }
     (void)p_atoms;
   }
@@ -448,6 +478,10 @@ int pt_attention_tc(const void* q, long long q_stride, const void* k, long long 
   a.heads = heads; a.Nq = Nq; a.Nk = Nk; a.NKP = (Nk + 15) & ~15;
   a.B = B; a.m_tiles = (Nq + kQRows - 1) / kQRows;
   a.scale_log2e = scale * 1.4426950408889634f;
+  {
+    const char* e = getenv("PT_ATTN_TRACE");              // developer hook: device address of 320 int64 (hex or decimal)
+    a.trace = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
+  }
   if ((out_stride & 7) || (reinterpret_cast<uintptr_t>(out) & 15))
     return pt::fail("pt_attention: out must be 16-byte aligned with a row stride multiple of 8 elements");
   CUtensorMap tq, tk, tv;

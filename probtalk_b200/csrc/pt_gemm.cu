@@ -303,8 +303,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (k2: the leader CTA issues for the pair)
-    if (lane == 0 && (!k2 || rank == 0)) {
+    // The WHOLE warp walks the loop (every lane waits on the same barriers) and one ELECTED lane issues: with
+    // `if (lane == 0)` around the loop the compiler cannot keep descriptors in uniform registers and wraps every
+    // tcgen05.mma in an election loop with five R2UR moves (~20 dependent instructions, ~70-100 cycles per MMA: as long
+    // as a 128 x 128 x 16 MMA takes to execute).  Descriptors advance by adding to their low word.
+    if (!k2 || rank == 0) {
       const uint32_t idesc = pt::umma_idesc_bf16(k2 ? 2 * BM : BM, BN);
+      const uint64_t da0 = pt::umma_desc_sw128(pt::smem_u32(smem));
+      const uint64_t db0 = pt::umma_desc_sw128(pt::smem_u32(smem) + C::kABytes);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
@@ -314,24 +320,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         for (int kk = 0; kk < p.K_iters; ++kk) {
           pt::mbar_wait(&full[stage], phase);
           pt::tc_fence_after();
-          const uint32_t sa = pt::smem_u32(smem + (size_t)stage * C::kStageBytes);
-          const uint32_t sb = sa + C::kABytes;
+          if (pt::elect_one()) {
+            const uint64_t so = (uint64_t)((uint32_t)stage * (uint32_t)(C::kStageBytes >> 4));
+            const uint64_t da = da0 + so, db = db0 + so;
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            if constexpr (k2)
-              pt::umma_bf16_2sm(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
-                                (kk | k) ? 1u : 0u);
-            else
-              pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128(sb + k * 32), idesc,
-                            (kk | k) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              if constexpr (k2)
+                pt::umma_bf16_2sm(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kk | k) ? 1u : 0u);
+              else
+                pt::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kk | k) ? 1u : 0u);
+            }
+            if constexpr (k2) {
+              pt::umma_commit_2sm(&empty[stage], 3);                  // both CTAs' slots are free
+              if (kk == p.K_iters - 1) pt::umma_commit_2sm(&tmem_full[acc], 3);   // both CTAs' accumulators are ready
+            } else {
+              pt::umma_commit(&empty[stage]);                         // slot reusable once these MMAs have read it
+              if (kk == p.K_iters - 1 && !(kRowNorm && p.res_mma)) pt::umma_commit(&tmem_full[acc]);
+            }
           }
-          if constexpr (k2) {
-            pt::umma_commit_2sm(&empty[stage], 3);                  // both CTAs' slots are free
-            if (kk == p.K_iters - 1) pt::umma_commit_2sm(&tmem_full[acc], 3);   // both CTAs' accumulators are ready
-          } else {
-            pt::umma_commit(&empty[stage]);                         // slot reusable once these MMAs have read it
-            if (kk == p.K_iters - 1 && !(kRowNorm && p.res_mma)) pt::umma_commit(&tmem_full[acc]);
-          }
+          __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
         if constexpr (kRowNorm) {
@@ -341,14 +348,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             for (int kb = 0; kb < 2; ++kb) {
               pt::mbar_wait(&full[stage], phase);
               pt::tc_fence_after();
-              const uint32_t sa = pt::smem_u32(smem + (size_t)stage * C::kStageBytes);
-              const uint32_t sb = sa + C::kABytes;
-              // one N = 256 instruction per K step: the four 64-column atoms of B are 8 KB apart (LBO)
+              if (pt::elect_one()) {
+                const uint32_t sa = pt::smem_u32(smem + (size_t)stage * C::kStageBytes);
+                const uint64_t da = pt::umma_desc_sw128(sa);
+                // one N = 256 instruction per K step: the four 64-column atoms of B are 8 KB apart (LBO)
+                const uint64_t db = pt::umma_desc_sw128_mn(sa + C::kABytes, 8192);
 #pragma unroll
-              for (int k = 0; k < BK / 16; ++k)
-                pt::umma_bf16(d_tmem, pt::umma_desc_sw128(sa + k * 32), pt::umma_desc_sw128_mn(sb + k * 2048, 8192), idesc_r, 1u);
-              pt::umma_commit(&empty[stage]);
-              if (kb == 1) pt::umma_commit(&tmem_full[acc]);
+                for (int k = 0; k < BK / 16; ++k)
+                  pt::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * (2048 >> 4)), idesc_r, 1u);
+                pt::umma_commit(&empty[stage]);
+                if (kb == 1) pt::umma_commit(&tmem_full[acc]);
+              }
+              __syncwarp();
               if (++stage == C::kStages) { stage = 0; phase ^= 1; }
             }
           }
