@@ -6,8 +6,8 @@
 //     P            = softmax(S)   one thread per query row, S read from TMEM, P written to smem as bf16 (K-major)
 //     O[128 x 64]  = P V          tcgen05.mma, V used in place as an MN-major operand (no transpose)
 // Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K and V, separate barriers), warp 1 = MMA issuer, warps 4-7 =
-// softmax (TMEM lane = query row), warps 8-11 = output (O read-out, 1/sum scaling, stores).  TMEM reads run at 64 B/clk
-// per SM and were the busiest unit (S read twice + O): setmaxnreg moves registers from warpgroup 0 to the softmax
+// softmax (TMEM lane = query row), warps 8-11 = output (O read-out, 1/sum scaling, stores).  Reading S twice (maximum, then exponentials) was the
+// busiest part of the row warps' work: setmaxnreg moves registers from warpgroup 0 to the softmax
 // warps so that up to 96 scores per row stay in registers and S is read ONCE; warps whose rows lie beyond Nq read nothing.
 // The unit chain (load -> Q K^T -> softmax -> P V -> store) is latency bound, so the stages are decoupled as far as the
 // buffers allow: the issuer thread POLLS two independent queues (next Q K^T, next P V) instead of blocking on either,
