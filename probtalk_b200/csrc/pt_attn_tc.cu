@@ -5,14 +5,16 @@
 //     S[128 x Nk]  = Q K^T        tcgen05.mma, Q and K straight from TMA (SWIZZLE_128B, K-major)
 //     P            = softmax(S)   one thread per query row, S read from TMEM, P written to smem as bf16 (K-major)
 //     O[128 x 64]  = P V          tcgen05.mma, V used in place as an MN-major operand (no transpose)
-// Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K and V, separate barriers), warp 1 = MMA issuer, warps 4-7 =
-// softmax (TMEM lane = query row), warps 8-11 = output (O read-out, 1/sum scaling, stores).  Reading S twice (maximum, then exponentials) was the
-// busiest part of the row warps' work: setmaxnreg moves registers from warpgroup 0 to the softmax
-// warps so that up to 96 scores per row stay in registers and S is read ONCE; warps whose rows lie beyond Nq read nothing.
+// Persistent CTAs: warp 0 = TMA producer (double-buffered Q/K and V, separate barriers), warp 1 = issuer of the Q K^T MMAs,
+// warp 2 = issuer of the P V MMAs, warps 4-7 = softmax (TMEM lane = query row), warps 8-11 = output (O read-out, 1/sum
+// scaling, stores).  Reading S twice (maximum, then exponentials) was the busiest part of the row warps' work: setmaxnreg
+// moves registers from warpgroup 0 to the softmax warps so that up to 96 scores per row stay in registers and S is read
+// ONCE; warps whose rows lie beyond Nq read nothing.
 // The unit chain (load -> Q K^T -> softmax -> P V -> store) is latency bound, so the stages are decoupled as far as the
-// buffers allow: the issuer thread POLLS two independent queues (next Q K^T, next P V) instead of blocking on either,
-// Q/K slots are released as soon as their Q K^T has run (not after P V), and V has its own full / empty barriers.  With
-// two S accumulators in TMEM the loads and the Q K^T of unit u+2 are in flight while unit u is still in its softmax.
+// buffers allow: the two MMA queues have their own issuer warps (each blocked on exactly its barriers; the whole warp walks
+// the loop and one elected lane issues), Q/K slots are released as soon as their Q K^T has run (not after P V), and V has
+// its own full / empty barriers.  With two S accumulators in TMEM the loads and the Q K^T of unit u+2 are in flight while
+// unit u is still in its softmax.
 #include <cuda.h>
 #include <stdlib.h>
 #include "pt_common.cuh"

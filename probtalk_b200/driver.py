@@ -148,6 +148,26 @@ class HolisticPipeline:
         return pred, codes
 
 
+    def infer_from_audio(self, features, waveform, labels, sampling_rate=16000, norm_stats=None, stand=False, noise=None):
+        """The whole of scripts/demo.py::infer between `librosa.load` and `get_vertices` (:104-205), on the device:
+        waveform [L] / [B, L] (16 kHz) -> wav2vec2 features at 30 fps (`features` = audio.Wav2Vec2Features, f1) ->
+        predictor windows, PQ-VAE decode, refiner windows (`windows_demo`) -> SMPL-X parameter rows (f2:
+        denormalize -> 6-D -> axis-angle -> part2full).  Returns (smplx [B, t, 265] , poses [B, 376, t], codes).
+        ``norm_stats``: the reference's (mean, std) pair of data_utils/norm_stats.npy, or None (no de-normalisation)."""
+        from . import postprocess as P
+        aud = features(waveform, sampling_rate=sampling_rate)
+        B = aud.shape[0]
+        labels = torch.as_tensor(labels, dtype=torch.int32, device=self.device).reshape(-1)
+        if labels.numel() == 1 and B > 1:
+            labels = labels.repeat(B)
+        poses, codes = self.windows_demo(aud, labels, noise=noise)
+        if norm_stats is not None:
+            smplx = P.poses_to_smplx(poses, norm_stats[0], norm_stats[1], P.c_index_6d(), stand=stand)
+        else:
+            smplx = P.poses_to_smplx(poses, stand=stand)
+        return smplx, poses, codes
+
+
 def run_sharded(n_units: int, compute, group=None):
     """Shard ``n_units`` independent clips/utterances over the ranks of ``group``; ``compute(start, end)`` returns
     this rank's result block [end-start, ...]; rank 0 gets the concatenation in unit order."""

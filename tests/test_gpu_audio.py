@@ -176,3 +176,23 @@ def test_features_facade_feeds_the_pipeline(hf_model):
         feats(wave, sampling_rate=22050)
     with pytest.raises(ValueError):
         feats(wave[:300])
+
+
+def test_demo_from_waveform(hf_model):
+    """scripts/demo.py::infer end to end on the device: waveform -> wav2vec2 features -> predictor / decode / refiner windows ->
+    SMPL-X rows, equal to the composition of its separately parity-tested parts."""
+    from probtalk_b200 import audio as A, driver as D, postprocess as P, synthetic as S
+    pipe = D.HolisticPipeline(S.make_vq_state(0), S.make_predictor_state(1), S.make_refiner_state(5))
+    feats = A.Wav2Vec2Features.from_hf(hf_model)
+    wave = S.synthetic_waveform(1, 16000 * 11, 21)[0]                       # 11 s -> t = 330 frames: 2 + 2 windows
+    g = torch.Generator(device="cuda").manual_seed(3)
+    aud = feats(wave)
+    assert aud.shape == (1, 768, 330)
+    n_tok = [pipe.predictor(1, e - s).N for s, e in D.demo_window_bounds(330, 180)]
+    noise = [(torch.rand(8, 1, n, device="cuda", generator=g),
+              -torch.log(-torch.log(torch.rand(8, 1, n, device="cuda", generator=g).clamp_(1e-10, 1 - 1e-7)))) for n in n_tok]
+    smplx, poses, codes = pipe.infer_from_audio(feats, wave, [2], noise=noise)
+    ref_poses, ref_codes = pipe.windows_demo(aud, torch.tensor([2], dtype=torch.int32, device="cuda"), noise=noise)
+    assert torch.equal(codes, ref_codes) and torch.equal(poses, ref_poses)
+    assert poses.shape == (1, 376, 330) and smplx.shape == (1, 330, 265) and bool(torch.isfinite(smplx).all())
+    assert torch.equal(smplx, P.poses_to_smplx(ref_poses))
