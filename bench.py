@@ -503,6 +503,8 @@ def run_extras(args, E, S, states, weights, dev, world, rank):
     # ---- f1: wav2vec2-base features of 60 s utterances (scripts/demo.py:105-111), 8 utterances per GPU
     # per call; random-init weights of the architecture (the checkpoint is not on the box); the reference's own
     # implementation (transformers, fp32) timed on the host cores for a bounded 10 s sample
+    if world > 1:          # (building the transformers model costs ~20 s of host time per rank: reported at N = 1 only)
+        return out
     try:
         from probtalk_b200 import audio as A
         model = S.make_wav2vec2(11)
