@@ -46,6 +46,11 @@ struct Cfg {
   static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256;   // + 24 KB static (epilogue staging)
 };
 
+#define GTRACE(role, tl, ev)                                                                                 \
+  do {                                                                                                       \
+    if (p.trace && blockIdx.x == 0 && (tl) < 16) p.trace[((role) * 16 + (tl)) * 8 + (ev)] = clock64();         \
+  } while (0)
+
 struct GemmKernelArgs {
   int M, N_tiles, K_iters;        // K_iters = taps * (C / 64)
   int c_iters;                    // C / 64
@@ -70,6 +75,7 @@ struct GemmKernelArgs {
   const int* labels;              // class per sample (row / label_rows) or null (class 0)
   int label_rows;
   int norm_classes;
+  long long* trace;               // developer hook (PT_GEMM_TRACE): clock64 stamps of CTA 0, [3 roles][16 tiles][8]
   int res_mma;                    // row-norm: the bf16 residual tile is added by the tensor core (identity x residual), tmap_r
   int tma_store;                  // tmap_o describes the output as a dense bf16 [M, n_valid] matrix: 32 x 32 boxes are stored by TMA
   // split-bf16 ("bf16x3") arithmetic: the K loop runs three passes  A_hi W_hi + A_hi W_lo + A_lo W_hi  (tmap_r = the lo
@@ -274,9 +280,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
+      int tl = 0;
+      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride, ++tl) {
         const int m0 = tile_m0(tile), n0 = tile_n0(tile);
+        GTRACE(0, tl, 0);
         for (int kk = 0; kk < p.K_iters; ++kk) {
+          if (kk == p.K_iters - 1) GTRACE(0, tl, 1);
           // split arithmetic: pass 0 = A_hi W_hi, pass 1 = A_hi W_lo (weight columns shifted by one K extent),
           // pass 2 = A_lo W_hi (A read through the lo plane's tensor map)
           int pass = 0, kq = kk;
@@ -299,6 +308,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
+        GTRACE(0, tl, 2);
       }
     }
   } else if (warp == 1) {
@@ -313,12 +323,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const uint64_t db0 = pt::umma_desc_sw128(pt::smem_u32(smem) + C::kABytes);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
+      int tl = 0;
+      for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride, ++tl) {
+        if (lane == 0) GTRACE(1, tl, 0);
         pt::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        if (lane == 0) GTRACE(1, tl, 1);
         pt::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kk = 0; kk < p.K_iters; ++kk) {
           pt::mbar_wait(&full[stage], phase);
+          if (lane == 0 && kk == 0) GTRACE(1, tl, 2);
+          if (lane == 0 && kk == p.K_iters - 1) GTRACE(1, tl, 3);
           pt::tc_fence_after();
           if (pt::elect_one()) {
             const uint64_t so = (uint64_t)((uint32_t)stage * (uint32_t)(C::kStageBytes >> 4));
@@ -364,6 +379,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             }
           }
         }
+        if (lane == 0) GTRACE(1, tl, 4);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -460,7 +476,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         }
         int cls = 0;
         if (p.labels) cls = min(max(__ldg(p.labels + min(m, p.M - 1) / p.label_rows), 0), p.norm_classes - 1);
+        if (e == 0 && lane == 0) GTRACE(2, it, 0);
         pt::mbar_wait(&tmem_full[acc], acc_phase);
+        if (e == 0 && lane == 0) GTRACE(2, it, 1);
         pt::tc_fence_after();
         const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
         uint32_t vr[kChunks][32];
@@ -470,6 +488,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         pt::tc_fence_before();
         __syncwarp();
         if (lane == 0) release_acc(acc);
+        if (e == 0 && lane == 0) GTRACE(2, it, 2);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         float f[kChunks][32];
         // ---- v = acc + bias (+ residual); per-row sum and sum of squares over this warp's 128 columns
@@ -530,7 +549,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         int ro4[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) ro4[j] = __shfl_sync(kFull, obase_m, pr + 8 * j);
+        if (e == 0 && lane == 0) GTRACE(2, it, 3);
         pt::mbar_wait(&stats_bar[par], (uint32_t)(it >> 1) & 1u);   // partials land in THIS CTA's smem: CTA-scope acquire
+        if (e == 0 && lane == 0) GTRACE(2, it, 4);
         float tsum = 0.f, tsq = 0.f;
 #pragma unroll
         for (int sidx = 0; sidx < 4; ++sidx) {             // fixed order: all four owners of a row get identical statistics
@@ -588,6 +609,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           if (lane == 0) pt::bulk_wait_read_all();
           __syncwarp();
         }
+        if (e == 0 && lane == 0) GTRACE(2, it, 5);
         continue;
       }
       __syncwarp();
@@ -1023,6 +1045,10 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   ka.oss = d->oss; ka.ors = d->ors; ka.ocs = d->ocs; ka.rss = d->rss; ka.rrs = d->rrs;
   ka.out = d->out; ka.bias = d->bias; ka.residual = d->residual; ka.out_f32 = d->out_f32; ka.res_f32 = d->res_f32;
   ka.act = d->act; ka.slope = d->slope; ka.m_tiles = (d->M + BM - 1) / BM;
+  {
+    const char* e = getenv("PT_GEMM_TRACE");              // developer hook: device address of 384 int64 (hex or decimal)
+    ka.trace = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
+  }
   ka.row_norm = d->row_norm; ka.norm_a = d->norm_a; ka.norm_b = d->norm_b; ka.labels = d->labels; ka.label_rows = d->label_rows; ka.norm_classes = d->norm_classes;
   cudaStream_t st = (cudaStream_t)stream;
   // Dense bf16 row-major outputs (every row of every sample valid, one pitch) are stored by TMA from the epilogue's
