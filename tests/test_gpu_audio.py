@@ -196,3 +196,29 @@ def test_demo_from_waveform(hf_model):
     assert torch.equal(codes, ref_codes) and torch.equal(poses, ref_poses)
     assert poses.shape == (1, 376, 330) and smplx.shape == (1, 330, 265) and bool(torch.isfinite(smplx).all())
     assert torch.equal(smplx, P.poses_to_smplx(ref_poses))
+
+
+def test_feature_error_downstream(hf_model):
+    """What the bf16 wav2vec2 path costs downstream: the same windows (teacher-forced codes, so that both runs decode the same
+    tokens) driven by our features and by the fp32 transformers features.  The refined poses differ by less than the
+    pipeline's own bf16 tolerance (refiner max-abs 0.038 / mean 0.0058)."""
+    from probtalk_b200 import audio as A, driver as D, synthetic as S
+    pipe = D.HolisticPipeline(S.make_vq_state(0), S.make_predictor_state(1), S.make_refiner_state(5))
+    feats = A.Wav2Vec2Features.from_hf(hf_model)
+    wave = S.synthetic_waveform(1, 16000 * 11, 22)
+    aud = feats(wave)
+    with torch.no_grad():
+        hid = hf_model(_normalise(wave)).last_hidden_state
+    aud_ref = F.interpolate(hid.transpose(1, 2), size=aud.shape[-1], mode="linear").cuda()
+    ids = torch.tensor([1], dtype=torch.int32, device="cuda")
+    poses, codes = pipe.windows_demo(aud, ids)
+    # teacher-force both runs with the codes of the first: window w covers code steps [19 w, 19 w + 22) of the concatenation
+    forced = []
+    for w, (s0, e0) in enumerate(D.demo_window_bounds(aud.shape[-1], 180)):
+        n = pipe.predictor(1, e0 - s0).N // codes.shape[-1]               # token steps of this window
+        forced.append(codes[:, 19 * w:19 * w + n].contiguous())
+    a, _ = pipe.windows_demo(aud, ids, force_codes=forced)
+    b, _ = pipe.windows_demo(aud_ref, ids, force_codes=forced)
+    d = (a - b).abs()
+    print("downstream of the feature error: poses max %.4f mean %.5f (|pose| mean %.3f)" % (d.max().item(), d.mean().item(), b.abs().mean().item()))
+    assert d.max().item() < 0.038 and d.mean().item() < 0.0058
