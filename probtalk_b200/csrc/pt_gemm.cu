@@ -228,26 +228,32 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // layout (rows = K); the A slot gets the matching 128 x 64 block of the identity, written by warp 3 (below).
     // 1.0 * bf16 accumulates exactly in fp32, and the epilogue no longer touches the residual at all.
     // full[] barriers take two arrivals in this flavour: the producer's (with the TMA byte count) and the filler's.
-    if (lane == 0) {
+    // The WHOLE warp walks the loop and one elected lane issues (see the plain producer below).
+    {
+      const int sh = p.s - 1;                              // s is 1 or 2: tap % s = tap & sh, tap / s = tap >> sh
       int stage = 0; uint32_t phase = 0;
       for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
         const int m0 = tile_m0(tile), n0 = tile_n0(tile);
+        int tap = 0, cc = 0;
         for (int kk = 0; kk < p.K_iters + 2; ++kk) {
           pt::mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
-          if (kk < p.K_iters) {
-            const int tap = kk / p.c_iters, cc = kk - tap * p.c_iters;
-            pt::mbar_expect_tx(&full[stage], C::kStageBytes);
-            pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
-            pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
-            pt::mbar_arrive(&full[stage]);                 // stands in for the filler's arrival
-          } else {
-            const int kb = kk - p.K_iters;
-            pt::mbar_expect_tx(&full[stage], C::kBBytes);
+          if (pt::elect_one()) {
+            uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+            if (kk < p.K_iters) {
+              pt::mbar_expect_tx(&full[stage], C::kStageBytes);
+              pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap & sh) * p.C, m0 + p.base_row + (tap >> sh));
+              pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
+              pt::mbar_arrive(&full[stage]);                 // stands in for the filler's arrival
+            } else {
+              const int kb = kk - p.K_iters;
+              pt::mbar_expect_tx(&full[stage], C::kBBytes);
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              pt::tma_load_2d(sa + C::kABytes + j * 8192, &tmap_r, &full[stage], n0 + 64 * j, m0 + 64 * kb);
+              for (int j = 0; j < BN / 64; ++j)
+                pt::tma_load_2d(sa + C::kABytes + j * 8192, &tmap_r, &full[stage], n0 + 64 * j, m0 + 64 * kb);
+            }
           }
+          __syncwarp();
+          if (++cc == p.c_iters) { cc = 0; ++tap; }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -278,37 +284,47 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
    } else if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // The WHOLE warp walks the loop (every lane waits on the slot's barrier) and one ELECTED lane issues, with (tap, channel
+    // block, pass) kept as counters.  The first version ran under `if (lane == 0)` and derived them by division: 156
+    // dependent instructions per K step (two integer divisions, an election loop with six R2UR moves around every
+    // UTMALDG), ~750 cycles -- longer than the 512 cycles the step's MMAs take.  PT_GEMM_TRACE showed the issuer waiting for
+    // operands all tile long, with activations resident in L2 or not: the GEMM ran at the pace of this thread.
+    {
+      const int sh = p.s - 1;                              // s is 1 or 2: tap % s = tap & sh, tap / s = tap >> sh
       int stage = 0; uint32_t phase = 0;
       int tl = 0;
       for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride, ++tl) {
         const int m0 = tile_m0(tile), n0 = tile_n0(tile);
-        GTRACE(0, tl, 0);
+        if (lane == 0) GTRACE(0, tl, 0);
+        // split arithmetic: pass 0 = A_hi W_hi, pass 1 = A_hi W_lo (weight columns shifted by one K extent),
+        // pass 2 = A_lo W_hi (A read through the lo plane's tensor map)
+        int pass = 0, kq = 0, tap = 0, cc = 0;
         for (int kk = 0; kk < p.K_iters; ++kk) {
-          if (kk == p.K_iters - 1) GTRACE(0, tl, 1);
-          // split arithmetic: pass 0 = A_hi W_hi, pass 1 = A_hi W_lo (weight columns shifted by one K extent),
-          // pass 2 = A_lo W_hi (A read through the lo plane's tensor map)
-          int pass = 0, kq = kk;
-          if (p.split) { pass = kk / p.k_base; kq = kk - pass * p.k_base; }
-          const int tap = kq / p.c_iters, cc = kq - tap * p.c_iters;
-          const int wcol = (pass == 1 ? kq + p.k_base : kq) * BK;
-          const CUtensorMap* tma = (pass == 2) ? &tmap_r : &tmap_a;
+          if (lane == 0 && kk == p.K_iters - 1) GTRACE(0, tl, 1);
           pt::mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
-          if constexpr (k2) {
-            // both CTAs' boxes complete on the leader's barrier: the leader arms it for the pair's bytes
-            if (rank == 0) pt::mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
-            pt::tma_load_2d_2sm(sa, tma, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
-            pt::tma_load_2d_2sm(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0 + (int)rank * (BN / 2));
-            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
-            continue;
+          if (pt::elect_one()) {
+            const int wcol = (pass == 1 ? kq + p.k_base : kq) * BK;
+            const CUtensorMap* tma = (pass == 2) ? &tmap_r : &tmap_a;
+            uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+            const int acol = cc * BK + (tap & sh) * p.C, arow = m0 + p.base_row + (tap >> sh);
+            if constexpr (k2) {
+              // both CTAs' boxes complete on the leader's barrier: the leader arms it for the pair's bytes
+              if (rank == 0) pt::mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+              pt::tma_load_2d_2sm(sa, tma, &full[stage], acol, arow);
+              pt::tma_load_2d_2sm(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0 + (int)rank * (BN / 2));
+            } else {
+              pt::mbar_expect_tx(&full[stage], C::kStageBytes);
+              pt::tma_load_2d(sa, tma, &full[stage], acol, arow);
+              pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0);
+            }
           }
-          pt::mbar_expect_tx(&full[stage], C::kStageBytes);
-          pt::tma_load_2d(sa, tma, &full[stage], cc * BK + (tap % p.s) * p.C, m0 + p.base_row + tap / p.s);
-          pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], wcol, n0);
+          __syncwarp();
+          ++kq;
+          if (++cc == p.c_iters) { cc = 0; ++tap; }
+          if (p.split && kq == p.k_base) { kq = 0; tap = 0; cc = 0; ++pass; }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        GTRACE(0, tl, 2);
+        if (lane == 0) GTRACE(0, tl, 2);
       }
     }
   } else if (warp == 1) {
@@ -584,8 +600,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             pk[2 * i + 1] = cvt_bf16x2(y2, y3, false);
           }
           if (p.tma_store) {
+            if (e == 0 && lane == 0 && c == 1) GTRACE(2, it, 6);
             if (lane == 0) pt::bulk_wait_read_all();     // the previous box has been read out of the tile
             __syncwarp();
+            if (e == 0 && lane == 0 && c == 1) GTRACE(2, it, 7);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
               *reinterpret_cast<uint4*>(tile_row[i]) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);

@@ -38,6 +38,6 @@ t0 = int(t[0, 0, 0])
 f = lambda x: int(x) - t0 if int(x) else None
 print(mode, "M =", M)
 print("per tile of CTA 0: producer [first load | last slot wait | loads issued]   issuer [wait acc | acc free | first operands | last operands | issued]"
-      "   epilogue warp 0 [wait acc | acc ready | acc read | stats sent | stats here | stored]")
+      "   epilogue warp 0 [wait acc | acc ready | acc read | stats sent | stats here | stored | chunk 1 ready | chunk 1 tile free]")
 for u in range(10):
-    print(u, [f(x) for x in t[0, u, :3]], [f(x) for x in t[1, u, :5]], [f(x) for x in t[2, u, :6]])
+    print(u, [f(x) for x in t[0, u, :3]], [f(x) for x in t[1, u, :5]], [f(x) for x in t[2, u, :8]])
