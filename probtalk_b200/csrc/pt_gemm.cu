@@ -35,15 +35,13 @@ constexpr int kThreads = (kEpiWarp0 + kEpiWarps) * 32;   // 384
 // (thread = row writes its 4 pieces; 4 lanes x 8 rows read / write global 64-byte segments) are bank-conflict free
 #define PT_TILE_OFF(r, piece) ((r) * 64 + ((((piece) ^ ((r) >> 1)) & 3) << 4))
 
-template <int BN, bool k2 = false, bool kRn = false>
+template <int BN, bool k2 = false>
 struct Cfg {
   // k2 (cta_group::2): each CTA of a pair stages its 128 rows of A and HALF of the BN weight rows
   static constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
   static constexpr uint32_t kBBytes = (k2 ? BN / 2 : BN) * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  // row-norm: three stages; the fourth's 48 KB buy every epilogue warp a second staging tile (its epilogue, not the
-  // operand ring, bounds that variant since the producer became cheap)
-  static constexpr int kStages = kRn ? 3 : (kStageBytes == 48 * 1024) ? 4 : 6;
+  static constexpr int kStages = (kStageBytes == 48 * 1024) ? 4 : 6;
   static constexpr uint32_t kTmemCols = 2 * BN;             // double-buffered accumulator
   static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 256;   // + 24 KB static (epilogue staging)
 };
@@ -158,7 +156,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_r,
             const GemmKernelArgs p) {
-  using C = Cfg<BN, k2, kRowNorm>;
+  using C = Cfg<BN, k2>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)C::kStages * C::kStageBytes);
@@ -169,7 +167,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   // epilogue staging lives in STATIC shared memory so the compiler emits LDS/STS (pointers carved from the
   // dynamic buffer lose their address space and become slow generic loads)
-  __shared__ __align__(1024) uint8_t tile_s[kEpiWarps * (kRowNorm ? 2 : 1)][32 * 64];   // PT_TILE_OFF == TMA SWIZZLE_64B, so a tile can be stored by TMA
+  __shared__ __align__(1024) uint8_t tile_s[kEpiWarps][32 * 64];   // PT_TILE_OFF == TMA SWIZZLE_64B, so a tile can be stored by TMA
   __shared__ __align__(16) float bias_s[kRowNorm ? 1 : kEpiWarps][BN / 2];   // this warp's 128 (or 64) bias columns of the current tile
   __shared__ long long rowoff_s[kRowNorm ? 1 : kEpiWarps][64];
   __shared__ __align__(16) float rn_bias_s[kRowNorm ? BN : 4];               // row-norm: the CTA's 256 bias columns
@@ -410,7 +408,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // covers whole 64-byte row segments (4 lanes x 16 B per row) instead of 32 different cache lines.
     const int e = warp - kEpiWarp0;
     const int q = e & 3, half = e >> 2;                  // TMEM lane quadrant (== warp % 4) and column half
-    uint8_t* tile = tile_s[kRowNorm ? 2 * e : e];        // [32 rows][4 swizzled 16-byte pieces]; row-norm: two of them, used in turn
+    uint8_t* tile = tile_s[e];                           // [32 rows][4 swizzled 16-byte pieces]
     long long* row_out = rowoff_s[kRowNorm ? 0 : e];                    // [32] output row offsets (or -1), [32] residual offsets
     long long* row_res = rowoff_s[kRowNorm ? 0 : e] + 32;
     int acc = 0; uint32_t acc_phase = 0;
@@ -602,19 +600,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             pk[2 * i + 1] = cvt_bf16x2(y2, y3, false);
           }
           if (p.tma_store) {
-            // two staging tiles per warp, used in turn: the store of chunk c - 1 may still be reading its tile while
-            // this chunk is written (chunk c - 2's store, the last user of THIS tile, must have read it)
-            const int tb = (c & 1) * 2048;
             if (e == 0 && lane == 0 && c == 1) GTRACE(2, it, 6);
-            if (lane == 0) pt::bulk_wait_read<1>();
+            if (lane == 0) pt::bulk_wait_read_all();     // the previous box has been read out of the tile
             __syncwarp();
             if (e == 0 && lane == 0 && c == 1) GTRACE(2, it, 7);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-              *reinterpret_cast<uint4*>(tile_row[i] + tb) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+              *reinterpret_cast<uint4*>(tile_row[i]) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
             pt::fence_async_smem();
             __syncwarp();
-            if (lane == 0) { pt::tma_store_2d(&tmap_o, tile + tb, n0 + cb + 32 * c, m0 + q * 32); pt::bulk_commit(); }
+            if (lane == 0) { pt::tma_store_2d(&tmap_o, tile, n0 + cb + 32 * c, m0 + q * 32); pt::bulk_commit(); }
             continue;
           }
           __syncwarp();
@@ -971,10 +966,10 @@ int launch_2cta(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap&
 
 // row-norm variant: clusters of two CTAs, one 128-row tile per cluster step
 int launch_rownorm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& tr, const GemmKernelArgs& ka, int sms, cudaStream_t st) {
-  PT_SMEM_OPT_IN((gemm_kernel<256, true, 1>), (Cfg<256, false, true>::kSmem));
+  PT_SMEM_OPT_IN((gemm_kernel<256, true, 1>), Cfg<256>::kSmem);
   int clusters = sms / 2;
   if (ka.m_tiles < clusters) clusters = ka.m_tiles;
-  PT_CUDA(pt::launch_pdl(gemm_kernel<256, true, 1>, dim3(2 * clusters), dim3(kThreads), Cfg<256, false, true>::kSmem, st, 2, ta, tb, to, tr, ka));
+  PT_CUDA(pt::launch_pdl(gemm_kernel<256, true, 1>, dim3(2 * clusters), dim3(kThreads), Cfg<256>::kSmem, st, 2, ta, tb, to, tr, ka));
   return 0;
 }
 
