@@ -341,7 +341,7 @@ def run_ours(args):
                 "roofline": {"bound": "tensor", "kernel": "gemm_kernel (tcgen05 bf16)", "achieved": ach, "peak": pk["tf_sust"],
                              "unit": "TFLOP/s", "frac": ach / pk["tf_sust"], "traffic": traffic,
                              "traffic_source": ("DRAM read+write bytes per GEMM launch, mean over the %d of %d launches of this "
-                                                "step whose shape is in profiles/r01_ncu_gemm_suite.csv (ncu --set full)"
+                                                "step whose shape is in profiles/r02_ncu_gemm_suite.csv (ncu --set full)"
                                                 % (traffic_hits, n_gemm)) if traffic else None,
                              "peak_source": pk["source"] + " bf16 sustained (kernel timed inside a long step)",
                              "launches_per_step": n_gemm, "gemm_ms_per_step": gemm_ms,
@@ -566,10 +566,10 @@ def profile_kernels(pred, ref):
 
 def gemm_traffic(keys):
     """DRAM bytes per GEMM launch (read + write), from the committed `ncu --set full` capture of the six transformer GEMM
-    shapes (profiles/r01_ncu_gemm_suite.csv, M = 90112; bytes scale with M for the refiner's M = 184320 launches).
+    shapes (profiles/r02_ncu_gemm_suite.csv, M = 90112; bytes scale with M for the refiner's M = 184320 launches).
     Average over the step's launches whose shape was captured; returns (bytes_per_launch, covered_launches)."""
     import csv
-    path = os.path.join(ROOT, "profiles", "r01_ncu_gemm_suite.csv")
+    path = os.path.join(ROOT, "profiles", "r02_ncu_gemm_suite.csv")
     try:
         rows = [r for r in csv.reader(open(path)) if r and not r[0].startswith("#")]
         hdr = rows[0]
