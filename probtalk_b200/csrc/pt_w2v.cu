@@ -99,6 +99,35 @@ __global__ void __launch_bounds__(kC0) w2v_fold_kernel(const double* __restrict_
   beff[(size_t)b * kC0 + c] = (float)((double)beta[c] - sc * mean - sc * r * mu * wsum);
 }
 
+// packed fp32x2 arithmetic (sm_100): both lanes are independent outputs (two adjacent channels)
+struct f2 { unsigned long long v; };
+__device__ __forceinline__ f2 pack2(float a, float b) { f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpack2(f2 x, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(x.v)); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// erf GELU of two values, 0.5 y (1 + erf(y / sqrt 2)), with erf from Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, far below
+// the bf16 rounding of the output): for z = |y| / sqrt 2,  erf z = 1 - t (a1 + t (a2 + t (a3 + t (a4 + t a5)))) exp(-z^2),
+// t = 1 / (1 + 0.3275911 z);  GELU = 0.5 y + 0.5 |y| - 0.5 |y| poly exp(-z^2).  Two MUFU ops + ~12 packed / scalar FMA-pipe
+// instructions per pair instead of two erff calls (~25 instructions each): this kernel is bound by instruction issue.
+__device__ __forceinline__ void gelu2(float y0, float y1, float& g0, float& g1) {
+  const float z0 = fabsf(y0) * 0.70710678118654752f, z1 = fabsf(y1) * 0.70710678118654752f;
+  const float t0 = rcp_approx(fmaf(0.3275911f, z0, 1.f)), t1 = rcp_approx(fmaf(0.3275911f, z1, 1.f));
+  const float e0 = ex2_approx(z0 * z0 * -1.4426950408889634f), e1 = ex2_approx(z1 * z1 * -1.4426950408889634f);
+  const f2 t = pack2(t0, t1);
+  f2 p = fma2(t, pack2(1.061405429f, 1.061405429f), pack2(-1.453152027f, -1.453152027f));
+  p = fma2(p, t, pack2(1.421413741f, 1.421413741f));
+  p = fma2(p, t, pack2(-0.284496736f, -0.284496736f));
+  p = fma2(p, t, pack2(0.254829592f, 0.254829592f));
+  p = mul2(mul2(p, t), pack2(e0, e1));                                     // poly(t) exp(-z^2) = 1 - erf z
+  const f2 h = pack2(0.5f * fabsf(y0), 0.5f * fabsf(y1));
+  const f2 lin = fma2(pack2(0.5f, 0.5f), pack2(y0, y1), h);                // 0.5 y + 0.5 |y|
+  const f2 nh = pack2(-0.5f * fabsf(y0), -0.5f * fabsf(y1));
+  unpack2(fma2(nh, p, lin), g0, g1);
+}
+
 constexpr int kTT = 64;                            // output frames per CTA of the conv pass
 __global__ void __launch_bounds__(256) w2v_conv0_kernel(const float* __restrict__ wave, long long L, long long T0,
                                                         const float* __restrict__ weff, const float* __restrict__ beff,
@@ -112,23 +141,22 @@ __global__ void __launch_bounds__(256) w2v_conv0_kernel(const float* __restrict_
     xs[i] = s < L ? x[s] : 0.f;
   }
   const int c = tid * 2;                           // two adjacent channels: one 4-byte store per frame, 128 B per warp
-  float w0[kK0], w1[kK0];
+  f2 w[kK0];                                       // (W'[c][j], W'[c + 1][j]) pairs: one packed FMA per tap for both channels
 #pragma unroll
-  for (int j = 0; j < kK0; ++j) {
-    w0[j] = weff[((size_t)b * kC0 + c) * kK0 + j];
-    w1[j] = weff[((size_t)b * kC0 + c + 1) * kK0 + j];
-  }
-  const float b0 = beff[(size_t)b * kC0 + c], b1 = beff[(size_t)b * kC0 + c + 1];
+  for (int j = 0; j < kK0; ++j) w[j] = pack2(weff[((size_t)b * kC0 + c) * kK0 + j], weff[((size_t)b * kC0 + c + 1) * kK0 + j]);
+  const f2 bias = pack2(beff[(size_t)b * kC0 + c], beff[(size_t)b * kC0 + c + 1]);
   __syncthreads();
   const int nt = (int)min((long long)kTT, T0 - tb);
   __nv_bfloat16* orow = out + ((size_t)b * rows_per_sample + tb) * kC0 + c;
+#pragma unroll 2
   for (int t = 0; t < nt; ++t) {
-    float y0 = b0, y1 = b1;
+    f2 y = bias;
 #pragma unroll
-    for (int j = 0; j < kK0; ++j) { const float v = xs[kS0 * t + j]; y0 = fmaf(w0[j], v, y0); y1 = fmaf(w1[j], v, y1); }
-    y0 = 0.5f * y0 * (1.f + erff(y0 * 0.70710678118654752f));
-    y1 = 0.5f * y1 * (1.f + erff(y1 * 0.70710678118654752f));
-    *reinterpret_cast<uint32_t*>(orow + (size_t)t * kC0) = pt::pack_bf16x2(y0, y1);
+    for (int j = 0; j < kK0; ++j) { const float v = xs[kS0 * t + j]; y = fma2(w[j], pack2(v, v), y); }
+    float y0, y1, g0, g1;
+    unpack2(y, y0, y1);
+    gelu2(y0, y1, g0, g1);
+    *reinterpret_cast<uint32_t*>(orow + (size_t)t * kC0) = pt::pack_bf16x2(g0, g1);
   }
 }
 
