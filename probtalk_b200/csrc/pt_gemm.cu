@@ -211,7 +211,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     if (p.res_mma || p.split) pt::tma_prefetch_desc(&tmap_r);
   }
   if (warp == 1 && lane == 0) {
-    const uint32_t full_count = (kRowNorm && p.res_mma) ? 2u : 1u;
+    const uint32_t full_count = 1u;
     for (int i = 0; i < C::kStages; ++i) { pt::mbar_init(&full[i], full_count); pt::mbar_init(&empty[i], kCL); }
     for (int i = 0; i < 2; ++i) { pt::mbar_init(&tmem_full[i], 1); pt::mbar_init(&tmem_empty[i], (k2 ? 2 : 1) * kEpiWarps); }
     if constexpr (kRowNorm) { pt::mbar_init(&stats_bar[0], kEpiWarps); pt::mbar_init(&stats_bar[1], kEpiWarps); }
@@ -239,9 +239,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // After the K blocks of a tile come two more pipeline slots that make the tensor core add the bf16 residual:
     //   acc[m, n] += sum_k I[m, k] * R[k, n],  k = row of the 128-row tile (two blocks of 64).
     // The B slot gets the residual rows as four [64 rows x 64 columns] boxes, which is exactly the MN-major operand
-    // layout (rows = K); the A slot gets the matching 128 x 64 block of the identity, written by warp 3 (below).
-    // 1.0 * bf16 accumulates exactly in fp32, and the epilogue no longer touches the residual at all.
-    // full[] barriers take two arrivals in this flavour: the producer's (with the TMA byte count) and the filler's.
+    // layout (rows = K); the A slot gets the matching 128 x 64 block of the identity, written by THIS warp's 32 lanes before
+    // the elected lane arms the barrier.  1.0 * bf16 accumulates exactly in fp32, and the epilogue no longer touches the
+    // residual at all.  (A separate filler warp used to write the identity and kept in step with the ring by waiting on the
+    // same `empty` barriers; a parity wait is only valid one phase ahead, and once the producer became fast a delayed
+    // filler could miss a whole phase of a K-block slot and dead-lock the CTA -- seen once in ~10^5 launches.)
     // The WHOLE warp walks the loop and one elected lane issues (see the plain producer below).
     {
       const int sh = p.s - 1;                              // s is 1 or 2: tap % s = tap & sh, tap / s = tap >> sh
@@ -251,13 +253,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         int tap = 0, cc = 0;
         for (int kk = 0; kk < p.K_iters + 2; ++kk) {
           pt::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
+          if (kk >= p.K_iters) {
+            // identity block of this residual slot: row m = 64 kb + r holds its 1.0 at column r (SWIZZLE_128B, K-major)
+            const int kb = kk - p.K_iters;
+            for (int i = lane; i < (int)(C::kABytes / 16); i += 32) reinterpret_cast<uint4*>(sa)[i] = make_uint4(0, 0, 0, 0);
+            __syncwarp();
+            for (int r = lane; r < 64; r += 32) {
+              const int m = 64 * kb + r;
+              *reinterpret_cast<uint16_t*>(sa + m * 128 + ((((r >> 3) ^ (m & 7)) & 7) << 4) + (r & 7) * 2) = 0x3F80;
+            }
+            pt::fence_async_smem();                        // generic-proxy writes -> visible to the tensor core's reads
+            __syncwarp();
+          }
           if (pt::elect_one()) {
-            uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
             if (kk < p.K_iters) {
               pt::mbar_expect_tx(&full[stage], C::kStageBytes);
               pt::tma_load_2d(sa, &tmap_a, &full[stage], cc * BK + (tap & sh) * p.C, m0 + p.base_row + (tap >> sh));
               pt::tma_load_2d(sa + C::kABytes, &tmap_b, &full[stage], kk * BK, n0);
-              pt::mbar_arrive(&full[stage]);                 // stands in for the filler's arrival
             } else {
               const int kb = kk - p.K_iters;
               pt::mbar_expect_tx(&full[stage], C::kBBytes);
@@ -270,30 +283,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           if (++cc == p.c_iters) { cc = 0; ++tap; }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-      }
-    }
-   } else if (warp == 3 && kRowNorm && p.res_mma) {
-    // ------------------------------------------------------------ identity filler (see above)
-    int stage = 0; uint32_t phase = 0;
-    for (int tile = tile_first; tile < n_tiles_total; tile += tile_stride) {
-      // walk the K-block slots in step with the producer (parity waits are only valid one phase ahead)
-      for (int kk = 0; kk < p.K_iters; ++kk) {
-        pt::mbar_wait(&empty[stage], phase ^ 1);
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
-      }
-      for (int kb = 0; kb < 2; ++kb) {
-        pt::mbar_wait(&empty[stage], phase ^ 1);
-        uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
-        for (int i = lane; i < (int)(C::kABytes / 16); i += 32) reinterpret_cast<uint4*>(sa)[i] = make_uint4(0, 0, 0, 0);
-        __syncwarp();
-        for (int r = lane; r < 64; r += 32) {              // row m = 64 kb + r holds its 1.0 at column r of this block
-          const int m = 64 * kb + r;
-          *reinterpret_cast<uint16_t*>(sa + m * 128 + ((((r >> 3) ^ (m & 7)) & 7) << 4) + (r & 7) * 2) = 0x3F80;
-        }
-        pt::fence_async_smem();
-        __syncwarp();
-        if (lane == 0) pt::mbar_arrive(&full[stage]);
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
    } else if (warp == 0) {
