@@ -452,6 +452,15 @@ def run_extras(args, E, S, states, weights, dev, world, rank):
     ms = _time_steps(cfg1, 20, warm=3)
     out["cfg1"] = {"ms_per_clip": ms, "clips_per_s": 1e3 / ms, "frames": 300, "batch": 1, "launches": enc.plan.launches + dec.plan.launches,
                    "what": "VQVAE_SC encode (split-bf16) -> PQ search -> fused gather+aft_vq -> decode (bf16), eager launches"}
+    # the same 39 launches replayed as one CUDA graph (what a latency-sensitive caller would do with a fixed clip length)
+    torch.cuda.synchronize()
+    g1 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g1):
+        enc.plan.run()
+        dec.plan.run()
+    ms_g = _time_steps(g1.replay, 50, warm=3)
+    out["cfg1"]["ms_per_clip_graph_replay"] = ms_g
+    del g1
     del enc, dec
     # ---- config 2: PQ nearest-code search microbench, 256 clips x 22 token steps x 4 groups; 16 distinct z buffers
     # (184 MB > the 126 MB L2) rotate so that every launch reads its z from HBM
