@@ -295,3 +295,27 @@ def test_gemm_rownorm_cluster_epilogue(M, K, mode):
         ops.gemm(a, w, out, M=M, C_=K, bias=bias, ors=N, residual=out, rrs=N, row_norm=2, norm_a=na, norm_b=nb)
         ref = F.layer_norm(v + x.float(), (N,), na[0], nb[0], 1e-5)
     assert (out.float() - ref).abs().max() < 0.06
+
+
+def test_gemm_rownorm_residual_many_launches():
+    """Soak of the residual-through-the-tensor-core flavour (row_norm 2, bf16 residual): a few hundred back-to-back launches
+    over many tiles per CTA must all complete (an earlier version dead-locked about once in 10^5 launches: a helper warp kept
+    in step with the operand ring through mbarrier parity waits and could be lapped by the producer) and give the same bits."""
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(77)
+    M, N, K = 90112, 512, 512
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    na, nb = torch.rand(1, N, device="cuda", generator=g) + 0.5, torch.randn(1, N, device="cuda", generator=g)
+    x = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    outs = []
+    for it in range(400):
+        out = torch.empty_like(x)
+        ops.gemm(a, w, out, M=M, C_=K, bias=bias, ors=N, residual=x, rrs=N, row_norm=2, norm_a=na, norm_b=nb)
+        if it in (0, 399):
+            outs.append(out)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], outs[1])
+    ref = F.layer_norm(a[:256].float() @ w.float().t() + bias + x[:256].float(), (N,), na[0], nb[0], 1e-5)
+    assert (outs[1][:256].float() - ref).abs().max() < 0.06
