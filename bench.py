@@ -175,6 +175,32 @@ class ReferenceCpu:
             return time.perf_counter() - t0
 
 
+def reference_cfg1(vq_state, reps=10):
+    """BASELINE config 1 on the host: one 300-frame clip through the UNMODIFIED reference PQ-VAE
+    (s2g_body_vqt: VQ.encoder -> vq_layer -> VQ.decode, vq_teacher.py:255-275), PyTorch CPU fp32; ms per clip or None."""
+    try:
+        from oracle import ref_harness as RH
+        from probtalk_b200 import synthetic as S
+        if not RH.reference_available():
+            return None
+        w = RH.build_vqt(vq_state)
+        x = S.synthetic_poses(1, 300, 1001)
+        with torch.no_grad():
+            def one():
+                z, _ = w.VQ.encoder(x)
+                qo = w.VQ.vq_layer(z, audio=None, label=None, load_pretrain=False)
+                return w.VQ.decode(qo.quantized, None)
+            for _ in range(3):
+                one()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                one()
+            return (time.perf_counter() - t0) / reps * 1e3
+    except Exception as e:
+        sys.stderr.write("reference arm: config 1 not timed (%s: %s)\n" % (type(e).__name__, e))
+        return None
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -199,7 +225,8 @@ def run_reference(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "config 4: predictor+refiner+PQ-VAE decode, one 180-frame window", "clips_per_step": Bs,
                        "frames": T_FRAMES, "full_batch_per_gpu": args.batch},
-            "cpu_baseline": dict({"value": v, "unit": "clips/s", "cores": cores, "kind": arm.kind, "sample": sample}, **info),
+            "cpu_baseline": dict({"value": v, "unit": "clips/s", "cores": cores, "kind": arm.kind, "sample": sample,
+                                  "cfg1_ms_per_clip": reference_cfg1(states[0])}, **info),
             "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
