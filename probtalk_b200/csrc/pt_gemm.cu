@@ -1042,8 +1042,9 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   int BN = d->row_norm ? 256
            : (d->N % 256 == 0 && ((long long)((d->M + BM - 1) / BM) * (d->N / 256)) >= sms) ? 256 : 128;
   {
-    const char* e = getenv("PT_GEMM_BN");                 // developer override: force 128-column tiles
+    const char* e = getenv("PT_GEMM_BN");                 // developer override: force 128- / 256-column tiles
     if (e && !d->row_norm && atoi(e) == 128) BN = 128;
+    if (e && !d->row_norm && atoi(e) == 256 && d->N % 256 == 0) BN = 256;
   }
   constexpr int CL = 1;
   // cta_group::2 pairs for the big plain GEMMs (PT_GEMM_2CTA=0 disables, for A/B measurements)
