@@ -138,6 +138,13 @@ typedef struct pt_gemm_desc {
   const void* a_lo;
   void* out_lo;
   const void* residual_lo;
+  /* grouped convolutions whose groups do not align with the 128-column output tiles (wav2vec2's positional convolution,
+   * transformers modeling_wav2vec2 Wav2Vec2PositionalConvEmbedding: Conv1d(768, 768, 128, groups = 16)): output tile j
+   * (columns [128 j, 128 j + 128)) reads its C input channels starting at column a_col_table[j] of A instead of 0, so
+   * that ONE launch covers every tile (W holds the tiles' zero-padded [128, taps*C] matrices one after the other).
+   * NULL, or a HOST array of N / 128 <= 8 ints, multiples of 8 with a_col_table[j] + C <= a_pitch; forces 128-column
+   * tiles; not with row_norm, split or s = 2. */
+  const int* a_col_table;
 } pt_gemm_desc;
 
 int pt_gemm_bf16(const pt_gemm_desc* desc, void* stream);

@@ -33,6 +33,7 @@ class GemmDesc(C.Structure):
         ("label_rows", C.c_int),
         ("norm_classes", C.c_int),
         ("split", C.c_int), ("a_lo", C.c_void_p), ("out_lo", C.c_void_p), ("residual_lo", C.c_void_p),
+        ("a_col_table", C.c_void_p),
     ]
 
 

@@ -12,8 +12,8 @@ with one recorded plan of C-ABI launches (``Wav2VecPlan``) over fixed device buf
     pt_gemm_bf16 x 6     conv1-4 (k3 s2), conv5-6 (k2 s2), GELU epilogue, valid convolution over token-major rows
     pt_layernorm_rows    feature_projection.layer_norm (512)
     pt_gemm_bf16         feature_projection.projection 512 -> 768 (twice: flat rows and the halo buffer of pos_conv)
-    pt_gemm_bf16 x 6     pos_conv_embed: Conv1d(768, 768, k128, pad 64, groups 16) + GELU as six 128-column output tiles,
-                         each a 128-tap contraction over the 192 input channels its (2-4) groups read
+    pt_gemm_bf16         pos_conv_embed: Conv1d(768, 768, k128, pad 64, groups 16) + GELU in one launch: six 128-column output
+                         tiles, each a 128-tap contraction over the 192 input channels its (2-4) groups read (a_col_table)
     pt_layernorm_rows    encoder.layer_norm(h + pos)
     12 x [ QKV GEMM (N = 2304), pt_attention (12 heads x 64, keys streamed), out-proj GEMM, LN(h + .),
            FF 768 -> 3072 GELU -> 768, LN(h + .) ]                       post-norm Wav2Vec2EncoderLayer
@@ -98,7 +98,7 @@ class Wav2VecWeights:
         wp, bp = _pos_conv_weight(sd), f("encoder.pos_conv_embed.conv.bias")
         cg = W2V_HIDDEN // W2V_POS_GROUPS
         assert tuple(wp.shape) == (W2V_HIDDEN, cg, W2V_POS_K), wp.shape
-        self.pos = []
+        tiles = []
         for j, off in enumerate(W2V_POS_OFFSETS):
             wm = torch.zeros(128, W2V_POS_K, 192)
             for n in range(128):
@@ -106,9 +106,11 @@ class Wav2VecWeights:
                 lo = cg * g - off
                 assert 0 <= lo and lo + cg <= 192
                 wm[n, :, lo:lo + cg] = wp[128 * j + n].t()
-            wt = _finish(wm, bp[128 * j:128 * (j + 1)], W2V_POS_K, 192, dev)
-            wt.cin = cg                                    # algorithmic FLOPs: 48 input channels per output channel
-            self.pos.append(wt)
+            tiles.append(wm)
+        # ONE weight matrix [768, 128 taps * 192]: the launch covers all six output tiles, tile j reading its 192-channel slab
+        # at column W2V_POS_OFFSETS[j] of the activations (pt_gemm_desc.a_col_table)
+        self.pos = _finish(torch.cat(tiles, 0), bp, W2V_POS_K, 192, dev)
+        self.pos.cin = cg                                  # algorithmic FLOPs: 48 input channels per output channel
         self.enc_ln = (vec("encoder.layer_norm.weight"), vec("encoder.layer_norm.bias"))
         self.layers = []
         for l in range(W2V_LAYERS):
@@ -174,9 +176,8 @@ class Wav2VecPlan:
                out_off=hb.H * H)
         # positional convolution + GELU (the k = 128 'same' convolution drops its last output frame)
         self.pos = Mat(M, H, dev)
-        for j, off in enumerate(W2V_POS_OFFSETS):
-            p.gemm(hb.t, B * hb.Tp, H, W.pos[j], self.pos.t, M=B * hb.Tp, C_=192, base_row=0, rows_per_sample=hb.Tp,
-                   t_valid=T, oss=T * H, ors=H, out_off=128 * j, act=ACT_GELU, a_off=off)
+        p.gemm(hb.t, B * hb.Tp, H, W.pos, self.pos.t, M=B * hb.Tp, C_=192, base_row=0, rows_per_sample=hb.Tp, t_valid=T,
+               oss=T * H, ors=H, act=ACT_GELU, a_col_table=list(W2V_POS_OFFSETS))
         ln = lambda x, res, gb, out: p.call(lib.pt_layernorm_rows, x.data_ptr(), None if res is None else res.data_ptr(),
                                             gb[0].data_ptr(), gb[1].data_ptr(), 1e-5, out.data_ptr(), M, H)
         mark("pos_conv", self.pos.t, T, T)

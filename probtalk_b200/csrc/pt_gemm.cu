@@ -75,6 +75,7 @@ struct GemmKernelArgs {
   const int* labels;              // class per sample (row / label_rows) or null (class 0)
   int label_rows;
   int norm_classes;
+  int a_col_tab[8];               // extra A column offset per 128-column output tile (grouped convolutions), zeros otherwise
   long long* trace;               // developer hook (PT_GEMM_TRACE): clock64 stamps of CTA 0, [3 roles][16 tiles][8]
   int res_mma;                    // row-norm: the bf16 residual tile is added by the tensor core (identity x residual), tmap_r
   int tma_store;                  // tmap_o describes the output as a dense bf16 [M, n_valid] matrix: 32 x 32 boxes are stored by TMA
@@ -309,7 +310,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             const int wcol = (pass == 1 ? kq + p.k_base : kq) * BK;
             const CUtensorMap* tma = (pass == 2) ? &tmap_r : &tmap_a;
             uint8_t* sa = smem + (size_t)stage * C::kStageBytes;
-            const int acol = cc * BK + (tap & sh) * p.C, arow = m0 + p.base_row + (tap >> sh);
+            const int acol = cc * BK + (tap & sh) * p.C + (BN == 128 ? p.a_col_tab[(n0 >> 7) & 7] : 0);
+            const int arow = m0 + p.base_row + (tap >> sh);
             if constexpr (k2) {
               // both CTAs' boxes complete on the leader's barrier: the leader arms it for the pair's bytes
               if (rank == 0) pt::mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
@@ -1011,7 +1013,16 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
   CUtensorMap ta, tb;
   // A viewed as [a_rows / s, s * C] (tap j of a stride-2 conv = row j/2, column half j%2)
   if (d->a_rows % d->s) return pt::fail("pt_gemm_bf16: a_rows (%lld) not divisible by stride", d->a_rows);
-  if (make_tmap(&ta, d->a, d->a_rows / d->s, (long long)d->s * d->C, (long long)d->s * d->a_pitch, BM)) return 1;
+  if (d->a_col_table) {
+    if (d->row_norm || d->split || d->s != 1 || d->N / 128 > 8)
+      return pt::fail("pt_gemm_bf16: a_col_table needs s = 1, N <= 1024, no row_norm, no split arithmetic");
+    for (int j = 0; j < d->N / 128; ++j)
+      if (d->a_col_table[j] < 0 || (d->a_col_table[j] & 7) || d->a_col_table[j] + d->C > d->a_pitch)
+        return pt::fail("pt_gemm_bf16: a_col_table[%d] = %d must be a multiple of 8 with offset + C <= a_pitch", j, d->a_col_table[j]);
+  }
+  // (with a column table the map spans the whole row pitch: every tile's slab lies inside it)
+  if (make_tmap(&ta, d->a, d->a_rows / d->s, d->a_col_table ? d->a_pitch : (long long)d->s * d->C, (long long)d->s * d->a_pitch, BM))
+    return 1;
   if (d->split) {
     if (d->row_norm) return pt::fail("pt_gemm_bf16: split arithmetic has no row_norm epilogue");
     if (!d->a_lo || (reinterpret_cast<uintptr_t>(d->a_lo) & 15)) return pt::fail("pt_gemm_bf16: split needs a 16-byte aligned a_lo plane");
@@ -1045,6 +1056,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     const char* e = getenv("PT_GEMM_BN");                 // developer override: force 128- / 256-column tiles
     if (e && !d->row_norm && atoi(e) == 128) BN = 128;
     if (e && !d->row_norm && atoi(e) == 256 && d->N % 256 == 0) BN = 256;
+    if (d->a_col_table) BN = 128;                          // the table is indexed by 128-column tile
   }
   constexpr int CL = 1;
   // cta_group::2 pairs for the big plain GEMMs (PT_GEMM_2CTA=0 disables, for A/B measurements)
@@ -1071,6 +1083,7 @@ extern "C" int pt_gemm_bf16(const pt_gemm_desc* d, void* stream) {
     const char* e = getenv("PT_GEMM_TRACE");              // developer hook: device address of 384 int64 (hex or decimal)
     ka.trace = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
   }
+  for (int j = 0; j < 8; ++j) ka.a_col_tab[j] = (d->a_col_table && j < d->N / 128) ? d->a_col_table[j] : 0;
   ka.row_norm = d->row_norm; ka.norm_a = d->norm_a; ka.norm_b = d->norm_b; ka.labels = d->labels; ka.label_rows = d->label_rows; ka.norm_classes = d->norm_classes;
   cudaStream_t st = (cudaStream_t)stream;
   // Dense bf16 row-major outputs (every row of every sample valid, one pitch) are stored by TMA from the epilogue's

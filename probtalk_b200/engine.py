@@ -253,9 +253,14 @@ class Plan:
     def gemm(self, a_t, a_rows, a_pitch, w: Weight, out_t, *, M, C_, s=1, base_row=0, rows_per_sample, t_valid,
              oss, ors, ocs=1, out_off=0, act=ACT_NONE, slope=0.2, residual=None, rss=0, rrs=0, res_off=0, a_off=0,
              n_valid=None, use_bias=True, row_norm=0, norm_a=None, norm_b=None, labels=None, label_rows=1,
-             a_lo=None, out_lo=None, residual_lo=None):
+             a_lo=None, out_lo=None, residual_lo=None, a_col_table=None):
         d = GemmDesc()
         d.a = a_t.data_ptr() + 2 * a_off
+        if a_col_table is not None:
+            # extra A column offset per 128-column output tile (grouped convolutions): a host array the call reads
+            tab = (C.c_int * len(a_col_table))(*a_col_table)
+            d.a_col_table = C.cast(tab, C.c_void_p)
+            self.keep.append(tab)
         if w.split:
             # split-bf16 arithmetic: every bf16 operand / result is a (hi, lo) plane pair
             assert a_lo is not None and row_norm == 0, "a split weight needs a split A operand"

@@ -88,7 +88,7 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
          residual: torch.Tensor = None, rss: int = 0, rrs: int = 0, res_offset: int = 0, act: int = ACT_NONE,
          slope: float = 0.2, a_rows: int = None, a_pitch: int = None, a_offset: int = 0, row_norm: int = 0,
          norm_a: torch.Tensor = None, norm_b: torch.Tensor = None, labels: torch.Tensor = None, label_rows: int = 1,
-         a_lo: torch.Tensor = None, out_lo: torch.Tensor = None, residual_lo: torch.Tensor = None):
+         a_lo: torch.Tensor = None, out_lo: torch.Tensor = None, residual_lo: torch.Tensor = None, a_col_table=None):
     """Launch the tensor-core contraction engine (see pt_gemm_bf16 in include/probtalk_b200.h).
     ``a`` / ``out`` / ``residual`` are flat device buffers; offsets are in elements.
     Split-bf16 arithmetic: pass ``a_lo`` (and ``out_lo`` / ``residual_lo`` for bf16 outputs / residuals) and a weight
@@ -99,6 +99,10 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M: int, C_: int
     split = a_lo is not None
     assert w.shape[1] == (2 if split else 1) * taps * C_ and w.is_contiguous()
     d = GemmDesc()
+    tab = None
+    if a_col_table is not None:                 # per-128-column-tile A column offsets (host ints), see pt_gemm_desc
+        tab = (C.c_int * len(a_col_table))(*a_col_table)
+        d.a_col_table = C.cast(tab, C.c_void_p)
     if split:
         d.split = 1
         d.a_lo = a_lo.data_ptr() + 2 * a_offset

@@ -32,10 +32,10 @@ def test_weight_packing(hf_model):
     win = xp.unfold(0, 128, 1)[:T]                                         # [T, 768, 128]: win[t, c, j] = xp[t + j, c]
     got = torch.empty(T, 768)
     for j, off in enumerate(A.W2V_POS_OFFSETS):
-        w = W.pos[j]
-        assert w.mat.shape == (128, 128 * 192) and w.n_valid == 128
+        w = W.pos                                                          # one [768, 128 taps * 192] matrix, tile j = rows 128 j ..
+        assert w.mat.shape == (768, 128 * 192) and w.n_valid == 768
         a = win[:, off:off + 192, :].permute(0, 2, 1).reshape(T, -1)       # tap-major, like the GEMM's K order
-        got[:, 128 * j:128 * (j + 1)] = a @ w.mat.float().t() + w.bias[:128]
+        got[:, 128 * j:128 * (j + 1)] = a @ w.mat[128 * j:128 * (j + 1)].float().t() + w.bias[128 * j:128 * (j + 1)]
     # bf16 weights: compare against the same convolution with bf16-rounded weights
     with torch.no_grad():
         ref16 = F.conv1d(x, conv.weight.bfloat16().float(), conv.bias, padding=64, groups=16)[:, :, :T]

@@ -222,3 +222,36 @@ def test_feature_error_downstream(hf_model):
     d = (a - b).abs()
     print("downstream of the feature error: poses max %.4f mean %.5f (|pose| mean %.3f)" % (d.max().item(), d.mean().item(), b.abs().mean().item()))
     assert d.max().item() < 0.038 and d.mean().item() < 0.0058
+
+
+def test_gemm_a_col_table_grouped_conv():
+    """pt_gemm_desc.a_col_table: one launch whose 128-column output tiles read different channel slabs of A -- a grouped
+    k = 5 'same' convolution (8 groups of 48 channels, 384 -> 384) against F.conv1d."""
+    from probtalk_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(9)
+    B, T, Cc, G, K = 2, 70, 384, 8, 5
+    cg = Cc // G
+    x = torch.randn(B, Cc, T, device="cuda", generator=g)
+    w = torch.randn(Cc, cg, K, device="cuda", generator=g) / (cg * K) ** 0.5
+    bias = torch.randn(Cc, device="cuda", generator=g)
+    H = K // 2
+    Tp = T + 2 * H
+    xf = torch.zeros(B, Tp, Cc, device="cuda")
+    xf[:, H:H + T] = x.transpose(1, 2)
+    xb = xf.bfloat16()
+    offs = (0, 96, 192)                              # tile j = outputs [128 j, 128 j + 128): groups 0-2, 2-5, 5-7; slab of 192 channels
+    wm = torch.zeros(Cc, K, 192, device="cuda")
+    for n in range(Cc):
+        j, grp = n // 128, n // cg
+        lo = cg * grp - offs[j]
+        assert 0 <= lo and lo + cg <= 192
+        wm[n, :, lo:lo + cg] = w[n].t()
+    wmat = wm.reshape(Cc, K * 192).bfloat16().contiguous()
+    out = torch.zeros(B, T, Cc, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(xb.view(-1), wmat, out.view(-1), M=B * Tp, C_=192, taps=K, base_row=0, rows_per_sample=Tp, t_valid=T,
+             oss=T * Cc, ors=Cc, bias=bias, a_pitch=Cc, a_rows=B * Tp, a_col_table=list(offs))
+    ref = F.conv1d(xb.float()[:, H:H + T].transpose(1, 2), w.bfloat16().float(), bias, padding=H, groups=G)
+    assert (out.float().transpose(1, 2) - ref).abs().max().item() < 0.03
+    with pytest.raises(Exception):                   # offset + C beyond the row pitch
+        ops.gemm(xb.view(-1), wmat, out.view(-1), M=B * Tp, C_=192, taps=K, base_row=0, rows_per_sample=Tp, t_valid=T,
+                 oss=T * Cc, ors=Cc, bias=bias, a_pitch=Cc, a_rows=B * Tp, a_col_table=[0, 96, 200])
