@@ -144,6 +144,25 @@ __device__ __forceinline__ float tanh_approx(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// erf GELU of two values in place (Abramowitz & Stegun 7.1.26, see apply_act): the polynomial runs as packed f32x2 FMAs
+__device__ __forceinline__ void gelu2(float& v0, float& v1) {
+  const float z0 = fabsf(v0) * 0.70710678118654752f, z1 = fabsf(v1) * 0.70710678118654752f;
+  float t0, t1, e0, e1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(fmaf(0.3275911f, z0, 1.f)));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(fmaf(0.3275911f, z1, 1.f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(z0 * z0 * -1.4426950408889634f));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(z1 * z1 * -1.4426950408889634f));
+  float p0, p1;
+  fma2(p0, p1, t0, t1, 1.061405429f, 1.061405429f, -1.453152027f, -1.453152027f);
+  fma2(p0, p1, p0, p1, t0, t1, 1.421413741f, 1.421413741f);
+  fma2(p0, p1, p0, p1, t0, t1, -0.284496736f, -0.284496736f);
+  fma2(p0, p1, p0, p1, t0, t1, 0.254829592f, 0.254829592f);
+  p0 *= t0 * e0; p1 *= t1 * e1;
+  const float h0 = 0.5f * fabsf(v0), h1 = 0.5f * fabsf(v1);
+  float l0, l1;
+  fma2(l0, l1, 0.5f, 0.5f, v0, v1, h0, h1);
+  fma2(v0, v1, -h0, -h1, p0, p1, l0, l1);
+}
 // two fp32 -> packed bf16x2 (low half = first argument), optionally clamped at zero by the conversion itself
 __device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi, bool relu) {
   uint32_t d;
@@ -422,8 +441,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // the common case (bf16 row-major output, no residual, identity / ReLU) gets a lean path: with K = 512 the
     // epilogue of a 128 x 256 tile has only ~4000 cycles before it starts to stall the tensor core
     const bool lean = row_major && !p.out_f32 && !p.residual && !kRowNorm && !p.split &&
-                      (p.act == PT_ACT_NONE || p.act == PT_ACT_RELU);
-    const bool lean_relu = (p.act == PT_ACT_RELU);
+                      (p.act == PT_ACT_NONE || p.act == PT_ACT_RELU || p.act == PT_ACT_GELU);
+    const bool lean_relu = (p.act == PT_ACT_RELU), lean_gelu = (p.act == PT_ACT_GELU);
     const int pr = lane >> 2, pc = lane & 3;             // piece mapping: row pr + 8*j, 16-byte piece pc
     // release an accumulator stage to the MMA issuer (k2: the issuer lives in the leader CTA)
     auto release_acc = [&](int acc_stage) {
@@ -697,6 +716,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
               add2(a0, a1, bb.x, bb.y);
               add2(a2, a3, bb.z, bb.w);
             }
+            if (lean_gelu) { gelu2(a0, a1); gelu2(a2, a3); }     // wav2vec2's convolutions and FF1 (erf GELU)
             pk[2 * i] = cvt_bf16x2(a0, a1, lean_relu);
             pk[2 * i + 1] = cvt_bf16x2(a2, a3, lean_relu);
           }
